@@ -1,0 +1,60 @@
+"""Imports the UNMODIFIED reference solvers from /root/reference (build container only).
+
+TEST INFRASTRUCTURE: used by oracle/make_golden.py and by tests that pin the C oracle against the live
+reference when /root/reference exists.  The GPU box has no /root/reference; nothing run there imports this.
+
+The reference package (`/root/reference/fmap2pointmap_solvers/__init__.py:1-8`) imports `gin`, which is not
+installed here; a no-op `gin.configurable` shim is injected so the reference code itself stays untouched.
+"""
+import importlib
+import os
+import sys
+import types
+
+REFERENCE_ROOT = os.environ.get("F2P_REFERENCE_ROOT", "/root/reference")
+
+
+def reference_available() -> bool:
+    return os.path.isfile(os.path.join(REFERENCE_ROOT, "fmap2pointmap_solvers", "naive.py"))
+
+
+def _gin_shim():
+    gin = types.ModuleType("gin")
+
+    def configurable(*args, **kwargs):
+        if args and callable(args[0]) and not kwargs:
+            return args[0]
+        return lambda fn: fn
+
+    gin.configurable = configurable
+    gin.REQUIRED = object()
+    return gin
+
+
+def load_reference():
+    """Returns the reference `fmap2pointmap_solvers` module object (not the drop-in of the same name)."""
+    if not reference_available():
+        raise RuntimeError(f"reference not found under {REFERENCE_ROOT}")
+    saved_gin = sys.modules.get("gin")
+    saved_pkg = {k: v for k, v in sys.modules.items() if k == "fmap2pointmap_solvers" or k.startswith("fmap2pointmap_solvers.")}
+    for k in saved_pkg:
+        del sys.modules[k]
+    if saved_gin is None:
+        sys.modules["gin"] = _gin_shim()
+    sys.path.insert(0, REFERENCE_ROOT)
+    try:
+        mod = importlib.import_module("fmap2pointmap_solvers")
+        sub = {k: v for k, v in sys.modules.items() if k.startswith("fmap2pointmap_solvers")}
+    finally:
+        sys.path.remove(REFERENCE_ROOT)
+        for k in list(sys.modules):
+            if k == "fmap2pointmap_solvers" or k.startswith("fmap2pointmap_solvers."):
+                del sys.modules[k]
+        sys.modules.update(saved_pkg)
+        if saved_gin is None:
+            del sys.modules["gin"]
+    # keep the reference modules alive under private names so pickling/inspection still works
+    for k, v in sub.items():
+        sys.modules["_f2p_reference." + k] = v
+    assert os.path.realpath(mod.__file__).startswith(os.path.realpath(REFERENCE_ROOT)), mod.__file__
+    return mod

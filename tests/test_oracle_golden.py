@@ -1,0 +1,114 @@
+"""CPU tests: the oracle (oracle/f2p_oracle.c and oracle/aten_port.py) against the golden vectors made from the
+unmodified reference, and against the live reference when /root/reference exists (build container only)."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_case
+from golden.cases import CASES
+from oracle import aten_port
+from oracle import f2p_oracle as O
+from oracle.ref_loader import load_reference, reference_available
+
+NAIVE = [n for n, c in CASES.items() if c["kind"] == "naive"]
+SPATIAL = [n for n, c in CASES.items() if c["kind"] == "spatial"]
+
+
+@pytest.mark.parametrize("name", NAIVE)
+def test_c_oracle_naive_matches_reference_golden(golden, name):
+    c, inp = load_case(golden, name)
+    got = O.naive(inp["C12"], inp["evecs_x"], inp["evecs_y"], int16_compat=True)
+    want = golden[name + "/p_pred"]
+    assert got.dtype == np.int64 and got.shape == want.shape
+    np.testing.assert_array_equal(got, want)
+
+
+@pytest.mark.parametrize("name", NAIVE)
+def test_c_oracle_intermediate_bits(golden, name):
+    """Projection and unclamped distance-GEMM bits (naive.py:20,33) are reproduced bit-for-bit."""
+    if name + "/feat_x" not in golden.files:
+        pytest.skip("intermediates stored for small cases only")
+    c, inp = load_case(golden, name)
+    feat = O.project(inp["evecs_x"], inp["C12"])
+    np.testing.assert_array_equal(feat.view(np.int32), golden[name + "/feat_x"].view(np.int32))
+    if name + "/d2_sample" in golden.files:
+        g = golden[name + "/d2_sample"]
+        ii, jj = np.meshgrid(np.arange(g.shape[0]), np.arange(g.shape[1]), indexing="ij")
+        d2, _ = O.pair_dist(feat, inp["evecs_y"], ii.ravel(), jj.ravel())
+        np.testing.assert_array_equal(d2.reshape(g.shape).view(np.int32), g.view(np.int32))
+
+
+@pytest.mark.parametrize("name", SPATIAL)
+def test_c_oracle_spatial_matches_reference_golden(golden, name):
+    c, inp = load_case(golden, name)
+    got, info = O.spatial(inp["C12"], inp["evecs_x"], inp["evecs_y"], inp["CAD"], inp["PC"], inp["diam_cad"],
+                          return_info=True)
+    np.testing.assert_array_equal(info["candidates"], golden[name + "/candidates"])
+    np.testing.assert_array_equal(got, golden[name + "/p_pred"])
+    assert info["skipped"] == bool(golden[name + "/skipped"])
+
+
+@pytest.mark.parametrize("name", ["naive_300x200_k30", "naive_duprows_600x400_k30", "naive_wrap_200x40000_k16",
+                                  "spatial_300x200_k30", "spatial_fallback065_600x200_k30",
+                                  "spatial_skipped_300x100_k30", "spatial_diamtensor_400x150_k30"])
+def test_aten_port_matches_reference_golden(golden, name, capsys):
+    c, inp = load_case(golden, name)
+    if c["kind"] == "naive":
+        got = aten_port.naive(inp["C12"], inp["evecs_x"], inp["evecs_y"])
+    else:
+        got = aten_port.spatial(inp["C12"], inp["evecs_x"], inp["evecs_y"], inp["CAD"], inp["PC"], inp["diam_cad"])
+    assert got.dtype == torch.int64
+    np.testing.assert_array_equal(got.numpy(), golden[name + "/p_pred"])
+    assert ("skipped" in capsys.readouterr().out) == bool(golden[name + "/skipped"])
+
+
+def test_duplicate_rows_pick_lowest_index(golden):
+    c, inp = load_case(golden, "naive_duprows_600x400_k30")
+    got = O.naive(inp["C12"], inp["evecs_x"], inp["evecs_y"])
+    assert (got[0] < c["n1"] // 2).all()
+
+
+def test_int16_wrap_row(golden):
+    c, inp = load_case(golden, "naive_wrap_200x40000_k16")
+    got = O.naive(inp["C12"], inp["evecs_x"], inp["evecs_y"], int16_compat=True)
+    assert got[1, 32767] == 32767 and got[1, 32768] == -32768 and got[1, 39999] == 39999 - 65536
+    plain = O.naive(inp["C12"], inp["evecs_x"], inp["evecs_y"], int16_compat=False)
+    np.testing.assert_array_equal(plain[1], np.arange(40000))
+    np.testing.assert_array_equal(plain[0], got[0])
+
+
+@pytest.mark.parametrize("M", [1, 5, 31, 32, 33, 255, 256, 257, 1000, 4099])
+def test_vote_cascade_order_matches_aten_sum(M):
+    """`.mean(0)` summation order (spacial_filtering.py:54): bitwise equal to ATen when ATen is fed IEEE sqrt values
+    (torch's own CPU sqrt is MKL VML and is not correctly rounded in ~0.7% of elements)."""
+    g = torch.Generator().manual_seed(100 + M)
+    X = torch.rand(M, 3, generator=g) * 10
+    Y = X @ torch.linalg.qr(torch.randn(3, 3, generator=g)).Q.t() + 0.3 * torch.randn(M, 3, generator=g)
+
+    def ed(t):
+        return torch.from_numpy(np.sqrt(torch.sum((t[:, None] - t) ** 2, dim=2).numpy()))
+
+    want = torch.absolute(ed(X) - ed(Y)).mean(0).numpy()
+    got = O.vote_scores(X, Y)
+    np.testing.assert_array_equal(got.view(np.int32), want.view(np.int32))
+
+
+@pytest.mark.parametrize("k", [1, 7, 8, 30, 33, 50, 64, 66, 128, 130, 256])
+def test_rownorm_order_matches_aten(k):
+    g = torch.Generator().manual_seed(k)
+    x = torch.randn(257, k, generator=g)
+    want = x.pow(2).sum(-1).numpy()
+    np.testing.assert_array_equal(O.rownorm(x).view(np.int32), want.view(np.int32))
+
+
+@pytest.mark.skipif(not reference_available(), reason="/root/reference only exists in the build container")
+@pytest.mark.parametrize("shape", [(257, 129, 30, 0), (900, 411, 50, 1), (1500, 64, 128, 2)])
+def test_c_oracle_matches_live_reference(shape):
+    from fmap2pointmap_solvers.synth import make_pair
+    n1, n2, k, seed = shape
+    ref = load_reference()
+    P = make_pair(n1, n2, k, seed=900 + seed)
+    want = ref.naive_fmap2pointmap(P.C12, P.evecs_x, P.evecs_y).numpy()
+    np.testing.assert_array_equal(O.naive(P.C12, P.evecs_x, P.evecs_y), want)
+    want = ref.spacial_filtering_fmap2pointmap(P.C12, P.evecs_x, P.evecs_y, P.CAD, P.PC, P.diam_cad).numpy()
+    np.testing.assert_array_equal(O.spatial(P.C12, P.evecs_x, P.evecs_y, P.CAD, P.PC, P.diam_cad), want)
