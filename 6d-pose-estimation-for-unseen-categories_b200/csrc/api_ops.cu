@@ -1,0 +1,124 @@
+// api_ops.cu — single-kernel C-ABI entry points (tests, roofline bench, host-side composition) and the
+// host-buffer convenience calls.  Declared in include/f2p.h.
+#include <string.h>
+#include <mutex>
+#include <vector>
+#include "common.cuh"
+#include "internal.h"
+
+using namespace f2p;
+
+namespace {
+
+int single_pair(PairDev& p, int n1, int n2, int ld1, int ld2, int nsplit_hint) {
+    memset(&p, 0, sizeof(p));
+    p.n1 = n1; p.n2 = n2;
+    p.nrt = (n1 + TILE - 1) / TILE; p.nct = (n2 + TILE - 1) / TILE;
+    if (ld1 < p.nrt * TILE || ld2 < p.nct * TILE || (ld1 % TILE) || (ld2 % TILE)) {
+        set_error("leading dimensions must be multiples of %d covering the padded extents (ld1=%d ld2=%d)", TILE, ld1, ld2);
+        return F2P_EINVAL;
+    }
+    p.nsplit = nsplit_hint;
+    return 0;
+}
+
+int pick_nsplit(int nrt, int nct) {
+    int dev = 0, sm = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev);
+    const int target = sm * 2 * 4;
+    int ns = 1;
+    if (nct > 0 && nct < target) ns = (target + nct - 1) / nct;
+    const int max_ns = nrt >= 4 ? nrt / 2 : 1;
+    if (ns > max_ns) ns = max_ns;
+    return ns < 1 ? 1 : ns;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t f2p_project_workspace_bytes(void) { return 256; }
+
+int f2p_project(const float* evecs, int n, int k, int ld_in, const float* C, float* xT, float* nrm, int ld,
+                void* ws, size_t ws_bytes, void* stream) {
+    if (!evecs || !xT || !nrm || !ws) { set_error("null pointer"); return F2P_EINVAL; }
+    if (k < 1 || k > F2P_MAX_K || n < 0 || ld_in < k) { set_error("bad shape n=%d k=%d ld_in=%d", n, k, ld_in); return k > F2P_MAX_K ? F2P_ENOTSUP : F2P_EINVAL; }
+    if (ws_bytes < 256) { set_error("workspace too small"); return F2P_ENOSPACE; }
+    PairDev p;
+    const bool is_x = (C != nullptr);
+    int rc = single_pair(p, is_x ? n : 1, is_x ? 0 : n, is_x ? ld : TILE, is_x ? 0 : ld, 1);
+    if (rc) return rc;
+    p.ldx = ld_in; p.ldy = ld_in;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    F2P_CUDA(cudaMemcpyAsync(ws, &p, sizeof(p), cudaMemcpyHostToDevice, st));
+    const int tiles = is_x ? p.nrt : p.nct;
+    return launch_project(is_x, evecs, C, static_cast<const PairDev*>(ws), 1, tiles, tiles, k, xT, ld, nrm, st);
+}
+
+size_t f2p_nn_workspace_bytes(int n1, int n2, int k, int top5) {
+    (void)k;
+    const int nrt = (n1 + TILE - 1) / TILE, nct = (n2 + TILE - 1) / TILE;
+    const int ns = pick_nsplit(nrt, nct);
+    size_t b = 256;
+    if (top5) b += sizeof(unsigned long long) * (size_t)nct * ns * TILE * 5;
+    else b += sizeof(unsigned long long) * (size_t)nct * TILE;
+    return (b + 255) & ~(size_t)255;
+}
+
+static int nn_common(int mode, const float* xT, const float* nx, int n1, int ld1, const float* yT, const float* ny,
+                     int n2, int ld2, int k, int64_t* out, void* ws_v, size_t ws_bytes, void* stream) {
+    if (!xT || !nx || !yT || !ny || !out || !ws_v) { set_error("null pointer"); return F2P_EINVAL; }
+    if (k < 1 || n1 < 1 || n2 < 0) { set_error("bad shape n1=%d n2=%d k=%d", n1, n2, k); return F2P_EINVAL; }
+    if (k > F2P_MAX_K) { set_error("k=%d exceeds F2P_MAX_K", k); return F2P_ENOTSUP; }
+    if (mode == 1 && n1 < F2P_TOPK) { set_error("top-5 needs n1 >= 5"); return F2P_ENOTSUP; }
+    if (n2 == 0) return 0;
+    if (ws_bytes < f2p_nn_workspace_bytes(n1, n2, k, mode)) { set_error("workspace too small"); return F2P_ENOSPACE; }
+    PairDev p;
+    const int nrt = (n1 + TILE - 1) / TILE, nct = (n2 + TILE - 1) / TILE;
+    int rc = single_pair(p, n1, n2, ld1, ld2, pick_nsplit(nrt, nct));
+    if (rc) return rc;
+    unsigned char* ws = static_cast<unsigned char*>(ws_v);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    F2P_CUDA(cudaMemcpyAsync(ws, &p, sizeof(p), cudaMemcpyHostToDevice, st));
+    const PairDev* pd = reinterpret_cast<const PairDev*>(ws);
+    unsigned long long* keys = reinterpret_cast<unsigned long long*>(ws + 256);
+    const int items = p.nct * p.nsplit;
+    // the single-op layout is the batch layout with one pair: ld*_total = ld*, but `best` is indexed by column
+    if (mode == 0) {
+        if ((size_t)ld2 > (size_t)nct * TILE) { /* best[] sized by nct*TILE: columns beyond are never touched */ }
+        rc = launch_nn(0, xT, ld1, nx, yT, ld2, ny, k, pd, 1, items, items, keys, nullptr, st);
+        if (rc) return rc;
+        // out: int64 [n2] only (row 0); reuse the batch finaliser into a temporary [2,n2]?  No: write row 0 in place.
+        return launch_finalize_argmin(keys, pd, 1, p.nct, p.nct, F2P_ROW0_ONLY, out, st);
+    }
+    rc = launch_nn(1, xT, ld1, nx, yT, ld2, ny, k, pd, 1, items, items, nullptr, keys, st);
+    if (rc) return rc;
+    return launch_finalize_top5(keys, pd, 1, p.nct, p.nct, F2P_ROW0_ONLY, out, 1, st);
+}
+
+int f2p_nn_argmin(const float* xT, const float* nx, int n1, int ld1, const float* yT, const float* ny, int n2, int ld2,
+                  int k, int64_t* idx_out, void* ws, size_t ws_bytes, void* stream) {
+    return nn_common(0, xT, nx, n1, ld1, yT, ny, n2, ld2, k, idx_out, ws, ws_bytes, stream);
+}
+int f2p_nn_top5(const float* xT, const float* nx, int n1, int ld1, const float* yT, const float* ny, int n2, int ld2,
+                int k, int64_t* idx5_out, void* ws, size_t ws_bytes, void* stream) {
+    return nn_common(1, xT, nx, n1, ld1, yT, ny, n2, ld2, k, idx5_out, ws, ws_bytes, stream);
+}
+
+size_t f2p_filter_workspace_bytes(int M) { return 256 + filter_pair_bytes(M < 0 ? 0 : M); }
+
+int f2p_spatial_filter(const float* cad, int ncad, const float* pc, int npc, const int64_t* p, int M,
+                       const float thr[4], int64_t* out, int32_t* count, int32_t* status, uint8_t* mask, float* scores,
+                       void* ws, size_t ws_bytes, void* stream) {
+    if (!cad || !pc || !p || !out || !count || !status || !ws || !thr) { set_error("null pointer"); return F2P_EINVAL; }
+    if (M < 0 || ncad < 1 || npc < 1) { set_error("bad shape M=%d ncad=%d npc=%d", M, ncad, npc); return F2P_EINVAL; }
+    if (M > 524288) { set_error("M > 524288 candidates unsupported"); return F2P_ENOTSUP; }
+    return run_filter_single(cad, ncad, pc, npc, p, M, thr, out, count, status, mask, scores,
+                             static_cast<unsigned char*>(ws), ws_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int f2p_measure_fp32_peak(double* packed, double* scalar, void* stream) {
+    return measure_fp32_peak(packed, scalar, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

@@ -1,0 +1,185 @@
+"""Batched host side of the B200 fmap->point-map path: packs a list of object/scene pairs into one C-ABI call
+(`f2p_naive_batched` / `f2p_spatial_batched`, include/f2p.h).  The per-sample Python loop of the reference
+(`scripts/eval.py:83-91`) becomes one launch sequence over all pairs; single-pair solver calls are batches of one.
+"""
+import ctypes
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import _lib
+
+_FACTORS = (0.3, 0.15, 0.055, 0.065)  # spacial_filtering.py:54,58,68-73
+
+
+def thresholds(diam_cad):
+    """The four `c * diam_cad` scalars exactly as torch forms them before comparing with an FP32 tensor:
+    Python/NumPy scalars multiply in FP64 and are then cast to FP32; FP32 tensors multiply in FP32."""
+    import numpy as np
+    if isinstance(diam_cad, torch.Tensor):
+        if diam_cad.numel() != 1:
+            raise ValueError("diam_cad must be a scalar")
+        if diam_cad.dtype == torch.float64:
+            d = float(diam_cad)
+            return [float(np.float32(c * d)) for c in _FACTORS]
+        d = np.float32(diam_cad.detach().float().cpu().item())
+        return [float(np.float32(np.float32(c) * d)) for c in _FACTORS]
+    d = float(diam_cad)
+    return [float(np.float32(c * d)) for c in _FACTORS]
+
+
+def _squeeze_c(C12):
+    # naive.py:17-18 / spacial_filtering.py:16-17
+    if C12.dim() == 3:
+        C12 = C12.squeeze(0)
+    if C12.dim() != 2 or C12.shape[0] != C12.shape[1]:
+        raise RuntimeError(f"C12 must be [K,K] or [1,K,K], got {tuple(C12.shape)}")
+    return C12
+
+
+class _Packed:
+    """Device views of a batch plus the descriptor array (offsets relative to per-operand base pointers)."""
+
+    def __init__(self, C_list, ex_list, ey_list, device, cad_list=None, pc_list=None, diam_list=None):
+        n = len(ex_list)
+        if not (len(C_list) == len(ey_list) == n):
+            raise ValueError("C12 / evecs_x / evecs_y lists differ in length")
+        self.n = n
+        self.keep = []  # keeps converted tensors alive until the call has been enqueued
+        Cs, exs, eys, cads, pcs = [], [], [], [], []
+        k = None
+        for i in range(n):
+            C = _lib.dev_f32(_squeeze_c(C_list[i]), device).contiguous()
+            ex = _lib.rowmajor_2d(_lib.dev_f32(ex_list[i], device))
+            ey = _lib.rowmajor_2d(_lib.dev_f32(ey_list[i], device))
+            if k is None:
+                k = int(C.shape[0])
+            if C.shape[0] != k or ex.shape[1] != k or ey.shape[1] != k:
+                raise RuntimeError(f"pair {i}: shapes {tuple(ex.shape)} @ {tuple(C.shape)}^T vs {tuple(ey.shape)} "
+                                   f"are inconsistent (all pairs of a batch must share K={k})")
+            Cs.append(C); exs.append(ex); eys.append(ey)
+            if cad_list is not None:
+                cad = _lib.dev_f32(cad_list[i], device).contiguous()
+                pc = _lib.dev_f32(pc_list[i], device).contiguous()
+                if cad.dim() != 2 or cad.shape[1] != 3 or pc.dim() != 2 or pc.shape[1] != 3:
+                    raise RuntimeError("CAD / PC must be [N,3]")
+                cads.append(cad); pcs.append(pc)
+        self.k = k if k is not None else 1
+        self.keep = [Cs, exs, eys, cads, pcs]
+        dummy = torch.zeros(4, dtype=torch.float32, device=device)
+        self.keep.append(dummy)
+
+        def base_of(ts):
+            # empty tensors have a null data_ptr: they contribute no base and get offset 0
+            return min((t.data_ptr() for t in ts if t.numel() > 0), default=dummy.data_ptr())
+
+        self.C_base, self.ex_base, self.ey_base = base_of(Cs), base_of(exs), base_of(eys)
+        self.cad_base, self.pc_base = base_of(cads), base_of(pcs)
+        self.descs = (_lib.F2PPairDesc * max(n, 1))()
+        self.out_sizes = []
+        out_off = 0
+        for i in range(n):
+            d = self.descs[i]
+            ex, ey = exs[i], eys[i]
+            d.evecs_x_off = (ex.data_ptr() - self.ex_base) // 4 if ex.numel() else 0
+            d.evecs_y_off = (ey.data_ptr() - self.ey_base) // 4 if ey.numel() else 0
+            d.c_off = (Cs[i].data_ptr() - self.C_base) // 4
+            d.n1, d.n2 = int(ex.shape[0]), int(ey.shape[0])
+            d.ldx = int(ex.stride(0)) if ex.shape[0] > 1 else self.k
+            d.ldy = int(ey.stride(0)) if ey.shape[0] > 1 else self.k
+            if cads:
+                d.cad_off = (cads[i].data_ptr() - self.cad_base) // 4 if cads[i].numel() else 0
+                d.pc_off = (pcs[i].data_ptr() - self.pc_base) // 4 if pcs[i].numel() else 0
+                d.ncad, d.npc = int(cads[i].shape[0]), int(pcs[i].shape[0])
+                thr = thresholds(diam_list[i])
+                for q in range(4):
+                    d.thr[q] = thr[q]
+                size = 10 * d.n2
+            else:
+                d.ncad, d.npc = d.n1, d.n2
+                size = 2 * d.n2
+            d.out_off = out_off
+            self.out_sizes.append(size)
+            out_off += size
+        self.out_total = out_off
+
+
+def naive_batched(C12: Sequence[torch.Tensor], evecs_x: Sequence[torch.Tensor], evecs_y: Sequence[torch.Tensor],
+                  int16_compat: bool = False) -> List[torch.Tensor]:
+    """`naive_fmap2pointmap` (naive.py:5-21) for a list of pairs sharing K: one int64 [2,V2] tensor per pair, on the
+    device of that pair's `evecs_x` (CPU inputs are copied to the current CUDA device and the result copied back)."""
+    lib = _lib.load()
+    n = len(evecs_x)
+    if n == 0:
+        return []
+    device = _lib.cuda_device_for(*evecs_x, *evecs_y, *C12)
+    with torch.cuda.device(device):
+        pk = _Packed(C12, evecs_x, evecs_y, device)
+        for i in range(n):
+            if pk.descs[i].n1 < 1:
+                raise RuntimeError(f"pair {i}: evecs_x has no rows (argmin of an empty dimension)")
+        out = torch.empty(max(pk.out_total, 1), dtype=torch.int64, device=device)
+        nbytes = lib.f2p_workspace_bytes(pk.descs, n, pk.k, 0)
+        if nbytes == 0:
+            _lib.check(-1 if pk.k <= _lib.F2P_MAX_K else -3, "f2p_workspace_bytes")
+        ws = _lib.workspace(device, nbytes)
+        rc = lib.f2p_naive_batched(pk.ex_base, pk.ey_base, pk.C_base, pk.descs, n, pk.k,
+                                   _lib.F2P_INT16_COMPAT if int16_compat else 0, out.data_ptr(), ws.data_ptr(),
+                                   ws.numel(), _lib.stream_ptr(device))
+        _lib.check(rc, "f2p_naive_batched")
+        res = []
+        for i in range(n):
+            d = pk.descs[i]
+            r = out[d.out_off:d.out_off + 2 * d.n2].view(2, d.n2)
+            src = evecs_x[i]
+            res.append(r if src.is_cuda else r.to(src.device))
+        return res
+
+
+def spatial_batched(C12: Sequence[torch.Tensor], evecs_x: Sequence[torch.Tensor], evecs_y: Sequence[torch.Tensor],
+                    CAD: Sequence[torch.Tensor], PC: Sequence[torch.Tensor], diam_cad: Sequence,
+                    int16_compat: bool = True, return_info: bool = False, verbose: bool = True):
+    """`spacial_filtering_fmap2pointmap` (spacial_filtering.py:4-75) for a list of pairs sharing K.
+    Returns one int64 [2,M'] tensor per pair (and, with return_info, per-pair dicts with the pre-filter candidates,
+    the "skipped" flag and the status word).  The one host sync is the read of the survivor counts."""
+    lib = _lib.load()
+    n = len(evecs_x)
+    if n == 0:
+        return ([], []) if return_info else []
+    device = _lib.cuda_device_for(*evecs_x, *evecs_y, *C12, *CAD, *PC)
+    with torch.cuda.device(device):
+        pk = _Packed(C12, evecs_x, evecs_y, device, CAD, PC, diam_cad)
+        out = torch.empty(max(pk.out_total, 1), dtype=torch.int64, device=device)
+        cand = torch.empty(max(pk.out_total, 1), dtype=torch.int64, device=device) if return_info else None
+        meta = torch.zeros(2 * n, dtype=torch.int32, device=device)
+        nbytes = lib.f2p_workspace_bytes(pk.descs, n, pk.k, 1)
+        if nbytes == 0:
+            # re-run the checks through the real entry point to get the precise message
+            rc = lib.f2p_spatial_batched(pk.ex_base, pk.ey_base, pk.C_base, pk.cad_base, pk.pc_base, pk.descs, n, pk.k, 0,
+                                         out.data_ptr(), meta.data_ptr(), meta.data_ptr() + 4 * n, None, out.data_ptr(),
+                                         0, _lib.stream_ptr(device))
+            _lib.check(rc if rc else -1, "f2p_spatial_batched")
+        ws = _lib.workspace(device, nbytes)
+        rc = lib.f2p_spatial_batched(pk.ex_base, pk.ey_base, pk.C_base, pk.cad_base, pk.pc_base, pk.descs, n, pk.k,
+                                     _lib.F2P_INT16_COMPAT if int16_compat else 0, out.data_ptr(), meta.data_ptr(),
+                                     meta.data_ptr() + 4 * n, cand.data_ptr() if cand is not None else None,
+                                     ws.data_ptr(), ws.numel(), _lib.stream_ptr(device))
+        _lib.check(rc, "f2p_spatial_batched")
+        host = meta.cpu()  # the unavoidable sync: M' sizes the returned tensors (spacial_filtering.py:68 syncs too)
+        res, infos = [], []
+        for i in range(n):
+            d = pk.descs[i]
+            m, status = int(host[i]), int(host[n + i])
+            if status & 2:
+                raise IndexError(f"pair {i}: candidate index out of range of CAD/PC (CAD rows {d.ncad}, PC rows {d.npc})")
+            M = 5 * d.n2
+            r = out[d.out_off:d.out_off + 2 * M].view(2, M)[:, :m].contiguous()
+            if status & 1 and verbose:
+                print("skipped")  # spacial_filtering.py:70-71
+            src = evecs_x[i]
+            res.append(r if src.is_cuda else r.to(src.device))
+            if return_info:
+                c = cand[d.out_off:d.out_off + 2 * M].view(2, M)
+                infos.append({"candidates": c if src.is_cuda else c.to(src.device), "skipped": bool(status & 1),
+                              "status": status})
+        return (res, infos) if return_info else res

@@ -1,0 +1,134 @@
+/*
+ * f2p.h — C-ABI of libf2p_sm100.so: B200 (sm_100a) functional-map -> point-map conversion.
+ *
+ * The reference has no FFI: its path is Python over ATen.  Every entry point below replaces a group of ATen
+ * call sites of /root/reference/fmap2pointmap_solvers (cited per function); the drop-in Python package
+ * `fmap2pointmap_solvers` binds them with ctypes (INTEGRATION.md shows the stub).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *   - *_dev pointers are device pointers on the current CUDA device, *_host pointers are host pointers;
+ *   - all floating data is FP32 row-major, all returned indices are int64 (the reference's dtype);
+ *   - every function returns 0 on success, a negative F2P_E* code on argument errors, or a positive
+ *     cudaError_t; f2p_last_error() returns a thread-local description;
+ *   - functions are asynchronous w.r.t. the host unless stated; the workspace must stay alive and must not
+ *     be shared by concurrent calls on different streams.
+ */
+#ifndef F2P_H_
+#define F2P_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define F2P_VERSION 100
+
+#define F2P_EINVAL   (-1)  /* bad argument (null pointer, negative size, k out of range)            */
+#define F2P_ENOSPACE (-2)  /* workspace too small                                                    */
+#define F2P_ENOTSUP  (-3)  /* shape outside the supported envelope (k > F2P_MAX_K, n > 2^31-129 ...) */
+#define F2P_EDEVICE  (-4)  /* not an sm_100 device / driver entry point missing                      */
+
+#define F2P_MAX_K 256      /* the reference's single-accumulator sgemm contract holds for k <= 256   */
+#define F2P_TOPK 5         /* K of spacial_filtering.py:33                                           */
+
+/* flags */
+#define F2P_INT16_COMPAT 1u /* row 1 = int16-wrapped point index, as naive.py:21 / spacial_filtering.py:36 */
+
+/* One object/scene pair of a batch.  Offsets are in ELEMENTS from the batch base pointers.
+ * (scripts/eval.py:83-87 is the per-sample loop this replaces.) */
+typedef struct F2PPairDesc {
+    int64_t evecs_x_off;  /* into evecs_x base: [n1,k] with row stride ldx */
+    int64_t evecs_y_off;  /* into evecs_y base: [n2,k] with row stride ldy */
+    int64_t c_off;        /* into C base: [k,k] contiguous                 */
+    int64_t cad_off;      /* into CAD base: [ncad,3] contiguous (spatial only) */
+    int64_t pc_off;       /* into PC base:  [npc,3] contiguous (spatial only)  */
+    int64_t out_off;      /* into out base: naive [2,n2]; spatial [2,5*n2] (row stride 5*n2) */
+    int32_t n1, n2;       /* rows of evecs_x / evecs_y                     */
+    int32_t ldx, ldy;     /* row strides of evecs_x / evecs_y in elements  */
+    int32_t ncad, npc;    /* rows of CAD / PC (>= n1 / n2; zero-padded rows allowed) */
+    float thr[4];         /* fl32(c*diam) for c = 0.3, 0.15, 0.055, 0.065 (spacial_filtering.py:54,58,68-73) */
+} F2PPairDesc;
+
+int f2p_version(void);
+const char* f2p_last_error(void);
+
+/* Device properties the host side needs for sizing (SM count, etc.). Returns 0 or an error. */
+int f2p_device_info(int* sm_count, int* cc_major, int* cc_minor, size_t* smem_optin);
+
+/* Workspace bytes for a batch with the given totals (sum over pairs of padded sizes is computed inside):
+ * spatial != 0 additionally reserves the top-5 and filter scratch. */
+size_t f2p_workspace_bytes(const F2PPairDesc* descs_host, int npairs, int k, int spatial);
+
+/* ---- whole-path entry points (device buffers) ------------------------------------------------------- */
+
+/* naive_fmap2pointmap (naive.py:5-21) for a batch of pairs sharing k.
+ * out[pair]: int64 [2,n2]: row 0 = argmin CAD row (lowest index on exact distance ties), row 1 = point index. */
+int f2p_naive_batched(const float* evecs_x_dev, const float* evecs_y_dev, const float* C_dev,
+                      const F2PPairDesc* descs_host, int npairs, int k, unsigned flags,
+                      int64_t* out_dev, void* ws_dev, size_t ws_bytes, void* stream);
+
+/* spacial_filtering_fmap2pointmap (spacial_filtering.py:4-75) for a batch of pairs sharing k.
+ * out[pair]: int64 [2,5*n2] buffer, survivors in columns [0,M'); counts_dev[pair] = M' (int32);
+ * status_dev[pair] bit0 = the reference would have printed "skipped" (spacial_filtering.py:70-71).
+ * cand_dev (optional, same layout as out) receives nn_query's [2,5*n2] candidates (spacial_filtering.py:22-40). */
+int f2p_spatial_batched(const float* evecs_x_dev, const float* evecs_y_dev, const float* C_dev,
+                        const float* cad_dev, const float* pc_dev,
+                        const F2PPairDesc* descs_host, int npairs, int k, unsigned flags,
+                        int64_t* out_dev, int32_t* counts_dev, int32_t* status_dev, int64_t* cand_dev,
+                        void* ws_dev, size_t ws_bytes, void* stream);
+
+/* ---- single-kernel entry points (device buffers; used by tests, bench roofline and the Python host) -- */
+
+/* Kernel 1: spectral projection (naive.py:20 / spacial_filtering.py:19) into the k-major operand layout:
+ * xT[c][i] = -2 * sum_b evecs[i,b]*C[c,b]  (sequential-b FMA, exact scaling), ld = leading dim (multiple of 128),
+ * nrm[i] = |feat_x[i]|^2 in ATen's summation order; columns i >= n are zero / nrm = +inf.
+ * C_dev == NULL transposes only (xT[c][i] = evecs[i,c], nrm = |row|^2, padding nrm = 0): the evecs_y operand. */
+int f2p_project(const float* evecs_dev, int n, int k, int ld_in, const float* C_dev,
+                float* xT_dev, float* nrm_dev, int ld, void* ws_dev, size_t ws_bytes, void* stream);
+
+/* Kernel 2: fused all-pairs squared distance + running arg-min (naive.py:33-34) over k-major operands.
+ * idx_out[j] (int64) = argmin_i sqrt(max(0, xT[:,i].yT[:,j] + nx[i] + ny[j])), lowest i on exact ties. */
+int f2p_nn_argmin(const float* xT_dev, const float* nx_dev, int n1, int ld1,
+                  const float* yT_dev, const float* ny_dev, int n2, int ld2, int k,
+                  int64_t* idx_out_dev, void* ws_dev, size_t ws_bytes, void* stream);
+
+/* Kernel 2b: same distances, 5 nearest rows per column ordered by (distance, index) (spacial_filtering.py:32-35).
+ * idx5_out[j*5+r] (int64). Requires n1 >= 5. */
+int f2p_nn_top5(const float* xT_dev, const float* nx_dev, int n1, int ld1,
+                const float* yT_dev, const float* ny_dev, int n2, int ld2, int k,
+                int64_t* idx5_out_dev, void* ws_dev, size_t ws_bytes, void* stream);
+
+/* Kernel 3: spatial-consistency filter (spacial_filtering.py:51-75) on candidate pairs p[2][M] (row stride M).
+ * Writes survivors to out[2][M] (row stride M), *count_dev = M', *status_dev bit0 = "skipped";
+ * mask_dev (optional, uint8 [M]) = 1 for surviving original columns; scores_dev (optional float [3][M]) = the
+ * per-round mean |A-B| of the columns alive in that round, in original column positions (others untouched). */
+int f2p_spatial_filter(const float* cad_dev, int ncad, const float* pc_dev, int npc,
+                       const int64_t* p_dev, int M, const float thr[4],
+                       int64_t* out_dev, int32_t* count_dev, int32_t* status_dev,
+                       uint8_t* mask_dev, float* scores_dev,
+                       void* ws_dev, size_t ws_bytes, void* stream);
+
+size_t f2p_project_workspace_bytes(void);
+size_t f2p_nn_workspace_bytes(int n1, int n2, int k, int top5);
+size_t f2p_filter_workspace_bytes(int M);
+
+/* ---- host-buffer convenience (what a non-torch caller binds; copies are inside the call) ------------- */
+
+/* Single pair, HOST pointers in and out; synchronous.  out_host: naive [2,n2]; spatial [2,5*n2] with *count. */
+int f2p_naive_host(const float* C_host, const float* evecs_x_host, int n1, const float* evecs_y_host, int n2,
+                   int k, unsigned flags, int64_t* out_host);
+int f2p_spatial_host(const float* C_host, const float* evecs_x_host, int n1, const float* evecs_y_host, int n2,
+                     int k, const float* cad_host, int ncad, const float* pc_host, int npc, const float thr[4],
+                     unsigned flags, int64_t* out_host, int32_t* count_host, int32_t* status_host);
+
+/* Measured FP32 FMA throughput of this device with the kernel-2 instruction mix (packed fma.rn.f32x2):
+ * runs ~ms of pure FMA work and returns TFLOP/s (roofline denominator next to the nominal figure). */
+int f2p_measure_fp32_peak(double* tflops_packed, double* tflops_scalar, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* F2P_H_ */

@@ -1,0 +1,218 @@
+"""GPU parity tests (run on the B200 box with `-m gpu`): the CUDA path, called through the drop-in Python API and the
+C-ABI, against the golden vectors of the real reference and against the CPU oracle on the same seeded inputs.
+Bar: bit-exact indices / masks / intermediate FP32 bits."""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_case
+from golden.cases import CASES
+
+pytestmark = pytest.mark.gpu
+
+NAIVE = [n for n, c in CASES.items() if c["kind"] == "naive"]
+SPATIAL = [n for n, c in CASES.items() if c["kind"] == "spatial"]
+
+
+@pytest.fixture(scope="module")
+def solvers():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import fmap2pointmap_solvers as S
+    from fmap2pointmap_solvers import _lib
+    _lib.load()  # must load the in-tree CUDA library: no fallback exists
+    return S
+
+
+@pytest.fixture(scope="module")
+def oracle():
+    from oracle import f2p_oracle as O
+    return O
+
+
+def _cuda(inp):
+    return {k: (v.cuda() if isinstance(v, torch.Tensor) and k != "diam_cad" else v) for k, v in inp.items()}
+
+
+# ---------------------------------------------------------------------------------------------- naive
+@pytest.mark.parametrize("name", NAIVE)
+def test_naive_matches_reference_golden(solvers, golden, name):
+    c, inp = load_case(golden, name)
+    d = _cuda(inp)
+    got = solvers.naive_fmap2pointmap(d["C12"], d["evecs_x"], d["evecs_y"], int16_compat=True)
+    assert got.dtype == torch.int64 and got.is_cuda and tuple(got.shape) == (2, c["n2"])
+    np.testing.assert_array_equal(got.cpu().numpy(), golden[name + "/p_pred"])
+
+
+def test_naive_cpu_inputs_roundtrip(solvers, golden):
+    """CPU tensors in -> H2D copy -> kernels -> result back on the CPU (the reference returns on the input device)."""
+    c, inp = load_case(golden, "naive_300x200_k30")
+    got = solvers.naive_fmap2pointmap(inp["C12"], inp["evecs_x"], inp["evecs_y"], CAD=None, PC=None, diam_cad=1.0)
+    assert not got.is_cuda
+    np.testing.assert_array_equal(got.numpy(), golden["naive_300x200_k30/p_pred"])
+
+
+def test_naive_default_row1_is_true_index(solvers, golden):
+    c, inp = load_case(golden, "naive_wrap_200x40000_k16")
+    d = _cuda(inp)
+    got = solvers.naive_fmap2pointmap(d["C12"], d["evecs_x"], d["evecs_y"]).cpu().numpy()
+    np.testing.assert_array_equal(got[1], np.arange(40000))
+    np.testing.assert_array_equal(got[0], golden["naive_wrap_200x40000_k16/p_pred"][0])
+
+
+def test_naive_requires_grad_and_noncontiguous(solvers, oracle):
+    from fmap2pointmap_solvers.synth import make_pair
+    P = make_pair(700, 300, 64, seed=77)
+    ex64 = torch.randn(700, 64)
+    ex64[:, :30] = P.evecs_x[:, :30]
+    C = P.C12[:30, :30].clone().cuda().requires_grad_(True)
+    ex = ex64.cuda()[:, :30]          # column-sliced view, row stride 64 (scripts/eval.py:87)
+    ey = P.evecs_y.cuda()[:, :30]
+    got = solvers.naive_fmap2pointmap(C, ex, ey).cpu().numpy()
+    want = oracle.naive(P.C12[:30, :30], ex64[:, :30], P.evecs_y[:, :30], int16_compat=False)
+    np.testing.assert_array_equal(got, want)
+
+
+@pytest.mark.parametrize("shape", [(1, 1, 1), (5, 1, 3), (127, 129, 17), (128, 128, 16), (129, 127, 15),
+                                   (1000, 3, 50), (3, 1000, 50), (777, 555, 100), (2500, 300, 256)])
+def test_naive_edge_shapes_vs_oracle(solvers, oracle, shape):
+    from fmap2pointmap_solvers.synth import make_pair
+    n1, n2, k = shape
+    P = make_pair(n1, n2, k, seed=500 + n1 + n2 + k)
+    got = solvers.naive_fmap2pointmap(P.C12.cuda(), P.evecs_x.cuda(), P.evecs_y.cuda()).cpu().numpy()
+    np.testing.assert_array_equal(got, oracle.naive(P.C12, P.evecs_x, P.evecs_y, int16_compat=False))
+
+
+def test_naive_errors(solvers):
+    with pytest.raises(RuntimeError):
+        solvers.naive_fmap2pointmap(torch.eye(4).cuda(), torch.randn(10, 5).cuda(), torch.randn(7, 4).cuda())
+    with pytest.raises(ValueError):
+        solvers.naive_fmap2pointmap(torch.eye(300).cuda(), torch.randn(10, 300).cuda(), torch.randn(7, 300).cuda())
+    out = solvers.naive_fmap2pointmap(torch.eye(4).cuda(), torch.randn(10, 4).cuda(), torch.zeros(0, 4).cuda())
+    assert tuple(out.shape) == (2, 0) and out.dtype == torch.int64
+
+
+def test_naive_batched_ragged(solvers, oracle):
+    from fmap2pointmap_solvers.synth import make_pair
+    shapes = [(300, 200), (1000, 64), (129, 500), (5, 5), (2048, 1024)]
+    Ps = [make_pair(a, b, 30, seed=40 + i) for i, (a, b) in enumerate(shapes)]
+    got = solvers.naive_batched([p.C12.cuda() for p in Ps], [p.evecs_x.cuda() for p in Ps], [p.evecs_y.cuda() for p in Ps])
+    for g, p in zip(got, Ps):
+        np.testing.assert_array_equal(g.cpu().numpy(), oracle.naive(p.C12, p.evecs_x, p.evecs_y, int16_compat=False))
+
+
+# ---------------------------------------------------------------------------------------------- spatial
+@pytest.mark.parametrize("name", SPATIAL)
+def test_spatial_matches_reference_golden(solvers, golden, name, capsys):
+    from fmap2pointmap_solvers.batched import spatial_batched
+    c, inp = load_case(golden, name)
+    d = _cuda(inp)
+    res, infos = spatial_batched([d["C12"]], [d["evecs_x"]], [d["evecs_y"]], [d["CAD"]], [d["PC"]], [d["diam_cad"]],
+                                 return_info=True)
+    np.testing.assert_array_equal(infos[0]["candidates"].cpu().numpy(), golden[name + "/candidates"])
+    got = solvers.spacial_filtering_fmap2pointmap(d["C12"], d["evecs_x"], d["evecs_y"], CAD=d["CAD"], PC=d["PC"],
+                                                  diam_cad=d["diam_cad"])
+    assert got.dtype == torch.int64 and got.is_cuda and got.shape[0] == 2
+    np.testing.assert_array_equal(got.cpu().numpy(), golden[name + "/p_pred"])
+    assert ("skipped" in capsys.readouterr().out) == bool(golden[name + "/skipped"])
+
+
+@pytest.mark.parametrize("shape", [(5, 1, 4), (40, 7, 8), (300, 33, 30), (600, 257, 30), (900, 410, 50), (3000, 820, 64)])
+def test_spatial_edge_shapes_vs_oracle(solvers, oracle, shape):
+    from fmap2pointmap_solvers.synth import make_pair
+    n1, n2, k = shape
+    P = make_pair(n1, n2, k, seed=700 + n1 + n2)
+    for scale in (1.0, 4.0):
+        diam = P.diam_cad * scale
+        got = solvers.spacial_filtering_fmap2pointmap(P.C12.cuda(), P.evecs_x.cuda(), P.evecs_y.cuda(), P.CAD.cuda(),
+                                                      P.PC.cuda(), diam).cpu().numpy()
+        np.testing.assert_array_equal(got, oracle.spatial(P.C12, P.evecs_x, P.evecs_y, P.CAD, P.PC, diam))
+
+
+def test_spatial_batched_ragged(solvers, oracle):
+    from fmap2pointmap_solvers.batched import spatial_batched
+    from fmap2pointmap_solvers.synth import make_pair
+    shapes = [(300, 200), (1000, 64), (129, 300), (50, 5), (2048, 700)]
+    Ps = [make_pair(a, b, 30, seed=60 + i) for i, (a, b) in enumerate(shapes)]
+    got = spatial_batched([p.C12.cuda() for p in Ps], [p.evecs_x.cuda() for p in Ps], [p.evecs_y.cuda() for p in Ps],
+                          [p.CAD.cuda() for p in Ps], [p.PC.cuda() for p in Ps], [p.diam_cad * 3 for p in Ps])
+    for g, p in zip(got, Ps):
+        np.testing.assert_array_equal(g.cpu().numpy(), oracle.spatial(p.C12, p.evecs_x, p.evecs_y, p.CAD, p.PC, p.diam_cad * 3))
+
+
+# ---------------------------------------------------------------------------------------------- C-ABI kernels
+def _ws(nbytes):
+    return torch.empty(int(nbytes) + 256, dtype=torch.uint8, device="cuda")
+
+
+@pytest.mark.parametrize("shape", [(300, 30), (1000, 50), (129, 7), (640, 128), (257, 256), (100, 1)])
+def test_kernel1_projection_and_norm_bits(solvers, oracle, shape):
+    from fmap2pointmap_solvers import _lib
+    L = _lib.load()
+    n, k = shape
+    g = torch.Generator().manual_seed(n * 7 + k)
+    e = torch.randn(n, k, generator=g) / n ** 0.5
+    C = torch.linalg.qr(torch.randn(k, k, generator=g)).Q.contiguous()
+    ld = (n + 127) // 128 * 128
+    xT = torch.full((k, ld), float("nan"), device="cuda")
+    nrm = torch.full((ld,), float("nan"), device="cuda")
+    ws = _ws(L.f2p_project_workspace_bytes())
+    ed, Cd = e.cuda(), C.cuda()
+    rc = L.f2p_project(ed.data_ptr(), n, k, k, Cd.data_ptr(), xT.data_ptr(), nrm.data_ptr(), ld, ws.data_ptr(), ws.numel(), None)
+    _lib.check(rc, "f2p_project")
+    torch.cuda.synchronize()
+    feat = oracle.project(e, C)
+    got = (-0.5 * xT[:, :n].t()).contiguous().cpu().numpy()
+    np.testing.assert_array_equal(got.view(np.int32), feat.view(np.int32))
+    np.testing.assert_array_equal(nrm[:n].cpu().numpy().view(np.int32), oracle.rownorm(feat).view(np.int32))
+    assert torch.isinf(nrm[n:]).all() and (xT[:, n:] == 0).all()
+    # transpose-only operand (evecs_y): C == NULL
+    rc = L.f2p_project(ed.data_ptr(), n, k, k, None, xT.data_ptr(), nrm.data_ptr(), ld, ws.data_ptr(), ws.numel(), None)
+    _lib.check(rc, "f2p_project")
+    torch.cuda.synchronize()
+    np.testing.assert_array_equal(xT[:, :n].t().contiguous().cpu().numpy().view(np.int32), e.numpy().view(np.int32))
+    np.testing.assert_array_equal(nrm[:n].cpu().numpy().view(np.int32), oracle.rownorm(e).view(np.int32))
+    assert (nrm[n:] == 0).all()
+
+
+@pytest.mark.parametrize("M", [1, 5, 31, 32, 33, 255, 256, 257, 1000, 4099, 9995])
+def test_kernel3_vote_scores_bits_and_mask(solvers, oracle, M):
+    from fmap2pointmap_solvers import _lib
+    from fmap2pointmap_solvers.batched import thresholds
+    L = _lib.load()
+    g = torch.Generator().manual_seed(1000 + M)
+    ncad, npc = 3 * M + 7, M + 3
+    CAD = torch.rand(ncad, 3, generator=g) * 10
+    Rm = torch.linalg.qr(torch.randn(3, 3, generator=g)).Q
+    p0 = torch.randint(0, ncad, (M,), generator=g)
+    p1 = torch.sort(torch.randint(0, npc, (M,), generator=g)).values
+    PC = torch.rand(npc, 3, generator=g) * 10
+    good = torch.rand(M, generator=g) < 0.6
+    PC[p1[good]] = CAD[p0[good]] @ Rm.t() + 0.05 * torch.randn(int(good.sum()), 3, generator=g)
+    p = torch.stack([p0, p1], 0).contiguous()
+    diam = 17.3
+    thr = (ctypes.c_float * 4)(*thresholds(diam))
+    out = torch.zeros(2, max(M, 1), dtype=torch.int64, device="cuda")
+    meta = torch.zeros(2, dtype=torch.int32, device="cuda")
+    mask = torch.zeros(max(M, 1), dtype=torch.uint8, device="cuda")
+    scores = torch.full((3, max(M, 1)), float("nan"), device="cuda")
+    ws = _ws(L.f2p_filter_workspace_bytes(M))
+    cd, pd, pp = CAD.cuda(), PC.cuda(), p.cuda()
+    rc = L.f2p_spatial_filter(cd.data_ptr(), ncad, pd.data_ptr(), npc, pp.data_ptr(), M, thr, out.data_ptr(),
+                              meta.data_ptr(), meta.data_ptr() + 4, mask.data_ptr(), scores.data_ptr(), ws.data_ptr(),
+                              ws.numel(), None)
+    _lib.check(rc, "f2p_spatial_filter")
+    torch.cuda.synchronize()
+    s0 = oracle.vote_scores(CAD[p0], PC[p1])
+    np.testing.assert_array_equal(scores[0, :M].cpu().numpy().view(np.int32), s0.view(np.int32))
+    want, info = oracle.spatial_filter(CAD, PC, p, diam, return_info=True)
+    m = int(meta[0])
+    assert m == want.shape[1]
+    np.testing.assert_array_equal(out[:, :m].cpu().numpy(), want)
+    assert bool(int(meta[1]) & 1) == info["skipped"]
+    keep = np.zeros(M, bool)
+    # survivors are a subsequence of the original columns
+    cols = {(int(a), int(b)) for a, b in want.T}
+    assert int(mask.sum()) == m
