@@ -79,7 +79,6 @@ static int build_plan(const F2PPairDesc* d, int npairs, int k, int spatial, bool
     if (k < 1) { set_error("k must be >= 1 (got %d)", k); return F2P_EINVAL; }
     if (k > F2P_MAX_K) { set_error("k=%d exceeds F2P_MAX_K=%d (the reference's sequential-k contract)", k, F2P_MAX_K); return F2P_ENOTSUP; }
     P.pairs.resize(npairs);
-    const int target_items = sm_count() * 2 * 4;
     int64_t base_items = 0;
     for (int i = 0; i < npairs; ++i) {
         if (d[i].n1 < 1 || d[i].n2 < 0) { set_error("pair %d: n1=%d n2=%d", i, d[i].n1, d[i].n2); return F2P_EINVAL; }
@@ -95,11 +94,7 @@ static int build_plan(const F2PPairDesc* d, int npairs, int k, int spatial, bool
         p.n1 = d[i].n1; p.n2 = d[i].n2; p.ldx = d[i].ldx; p.ldy = d[i].ldy; p.ncad = d[i].ncad; p.npc = d[i].npc;
         memcpy(p.thr, d[i].thr, sizeof(p.thr));
         p.nrt = (p.n1 + TILE - 1) / TILE; p.nct = (p.n2 + TILE - 1) / TILE;
-        int ns = 1;
-        if (base_items > 0 && base_items < target_items) ns = (int)((target_items + base_items - 1) / base_items);
-        const int max_ns = p.nrt >= 4 ? p.nrt / 2 : (p.nrt > 0 ? 1 : 1);
-        if (ns > max_ns) ns = max_ns;
-        if (ns < 1) ns = 1;
+        const int ns = choose_nsplit(base_items, p.nrt, sm_count());
         p.nsplit = ns;
         if (P.ld1_total + p.nrt * (int64_t)TILE > 0x7fffff00ll || P.ld2_total + p.nct * (int64_t)TILE > 0x7fffff00ll ||
             (int64_t)P.total_items + (int64_t)p.nct * ns > 0x7fffff00ll) {

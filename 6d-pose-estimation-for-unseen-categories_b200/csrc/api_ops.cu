@@ -25,12 +25,7 @@ int single_pair(PairDev& p, int n1, int n2, int ld1, int ld2, int nsplit_hint) {
 int pick_nsplit(int nrt, int nct) {
     int dev = 0, sm = 148;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev);
-    const int target = sm * 2 * 4;
-    int ns = 1;
-    if (nct > 0 && nct < target) ns = (target + nct - 1) / nct;
-    const int max_ns = nrt >= 4 ? nrt / 2 : 1;
-    if (ns > max_ns) ns = max_ns;
-    return ns < 1 ? 1 : ns;
+    return choose_nsplit(nct, nrt, sm);
 }
 
 }  // namespace

@@ -4,6 +4,21 @@
 
 namespace f2p {
 
+// Row splits per column tile.  Two goals: (1) at least ~2 waves of CTAs (2 CTAs/SM) even for one small pair, with
+// >= 2 row tiles per item; (2) for big problems ~40 waves so the last partial wave costs < 3%, while every item still
+// streams >= 16 row tiles (amortises the resident column-operand load and the final cross-thread reduction).
+static inline int choose_nsplit(long long base_items, int nrt, int sm) {
+    if (base_items <= 0 || nrt <= 1) return 1;
+    const long long slots = 2ll * sm;
+    long long ns1 = (2 * slots + base_items - 1) / base_items;
+    long long ns2 = (40 * slots + base_items - 1) / base_items;
+    const long long cap1 = nrt / 2 > 0 ? nrt / 2 : 1, cap2 = nrt / 16 > 0 ? nrt / 16 : 1;
+    if (ns1 > cap1) ns1 = cap1;
+    if (ns2 > cap2) ns2 = cap2;
+    long long ns = ns1 > ns2 ? ns1 : ns2;
+    return (int)(ns < 1 ? 1 : ns);
+}
+
 // prep.cu
 int launch_project(bool is_x, const float* evecs, const float* Cmat, const PairDev* pairs_dev, int npairs,
                    int uniform_tiles, int total_tiles, int k, float* outT, int64_t ld_total, float* nrm,
