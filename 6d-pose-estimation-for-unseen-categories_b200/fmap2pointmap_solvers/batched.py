@@ -13,19 +13,20 @@ _FACTORS = (0.3, 0.15, 0.055, 0.065)  # spacial_filtering.py:54,58,68-73
 
 
 def thresholds(diam_cad):
-    """The four `c * diam_cad` scalars exactly as torch forms them before comparing with an FP32 tensor:
-    Python/NumPy scalars multiply in FP64 and are then cast to FP32; FP32 tensors multiply in FP32."""
+    """The four `c * diam_cad` scalars exactly as the reference's comparison sees them: the product is formed by the
+    host language with `diam_cad`'s own type (Python/NumPy float -> FP64 product; FP32 tensor -> FP32 product), then
+    torch casts it to the FP32 compare type."""
     import numpy as np
-    if isinstance(diam_cad, torch.Tensor):
-        if diam_cad.numel() != 1:
-            raise ValueError("diam_cad must be a scalar")
-        if diam_cad.dtype == torch.float64:
-            d = float(diam_cad)
-            return [float(np.float32(c * d)) for c in _FACTORS]
-        d = np.float32(diam_cad.detach().float().cpu().item())
-        return [float(np.float32(np.float32(c) * d)) for c in _FACTORS]
-    d = float(diam_cad)
-    return [float(np.float32(c * d)) for c in _FACTORS]
+    out = []
+    for c in _FACTORS:
+        v = c * diam_cad          # the reference's own expression (spacial_filtering.py:54): host-side type rules apply
+        if isinstance(v, torch.Tensor):
+            if v.numel() != 1:
+                raise ValueError("diam_cad must be a scalar")
+            out.append(float(v.detach().to(torch.float32).cpu().item()))   # 0-d tensors are cast to the FP32 compare type
+        else:
+            out.append(float(np.float32(float(v))))                       # wrapped number -> FP32 compare type
+    return out
 
 
 def _squeeze_c(C12):

@@ -1,0 +1,82 @@
+"""Pair-sharded multi-GPU driver: one process per GPU, contiguous pair slices, one all-gather to return index maps.
+
+The reference has no distributed code; pairs are independent (`scripts/eval.py:83`), so the path shards
+with no data-path collective.  The only exchange is returning the int64 index maps to every rank: NCCL all-gather over
+NVLink on a B200 box, gloo in the CPU tests (which inject a compute function; the product compute is CUDA only).
+"""
+from typing import Callable, List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+
+def shard_range(n_items: int, world_size: int, rank: int) -> Tuple[int, int]:
+    """Contiguous slice [lo, hi) of ceil(n/world) items per rank."""
+    per = (n_items + world_size - 1) // world_size if world_size > 0 else n_items
+    lo = min(rank * per, n_items)
+    return lo, min(lo + per, n_items)
+
+
+def pack_maps(maps: Sequence[torch.Tensor], widths: Sequence[int], per_rank: int, device) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Packs this rank's [2,M_i] maps into a fixed [per_rank, 2, Wmax] int64 payload (−1 padded) plus counts."""
+    wmax = max(list(widths) + [1])
+    payload = torch.full((per_rank, 2, wmax), -1, dtype=torch.int64, device=device)
+    counts = torch.full((per_rank,), -1, dtype=torch.int64, device=device)
+    for i, m in enumerate(maps):
+        payload[i, :, :m.shape[1]] = m.to(device)
+        counts[i] = m.shape[1]
+    return payload, counts
+
+
+def solve_sharded(solver: str, C12: Sequence[torch.Tensor], evecs_x: Sequence[torch.Tensor],
+                  evecs_y: Sequence[torch.Tensor], CAD: Optional[Sequence[torch.Tensor]] = None,
+                  PC: Optional[Sequence[torch.Tensor]] = None, diam_cad: Optional[Sequence] = None,
+                  group=None, compute: Optional[Callable] = None, device=None) -> List[torch.Tensor]:
+    """Every rank passes the SAME global pair list (or at least its own slice populated); each converts its slice and
+    all ranks return the full list of index maps in global pair order.
+
+    solver: "naive" | "spatial".  `compute(solver, C, ex, ey, cad, pc, diam) -> list of [2,M]` defaults to the CUDA path.
+    """
+    if solver not in ("naive", "spatial"):
+        raise ValueError("solver must be 'naive' or 'spatial'")
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    n = len(evecs_x)
+    lo, hi = shard_range(n, world, rank)
+    per = (n + world - 1) // world if world > 0 else n
+    if compute is None:
+        from .batched import naive_batched, spatial_batched
+
+        def compute(kind, C, ex, ey, cad, pc, diam):
+            if kind == "naive":
+                return naive_batched(C, ex, ey)
+            return spatial_batched(C, ex, ey, cad, pc, diam, verbose=False)
+    sl = slice(lo, hi)
+    mine = compute(solver, list(C12[sl]), list(evecs_x[sl]), list(evecs_y[sl]),
+                   list(CAD[sl]) if CAD is not None else None, list(PC[sl]) if PC is not None else None,
+                   list(diam_cad[sl]) if diam_cad is not None else None) if hi > lo else []
+    if world == 1:
+        return list(mine)
+    if device is None:
+        device = mine[0].device if mine else (torch.device("cuda", torch.cuda.current_device())
+                                              if torch.cuda.is_available() and dist.get_backend(group) == "nccl"
+                                              else torch.device("cpu"))
+    # payload width: fixed by the global shapes so every rank agrees without an extra exchange
+    mult = 1 if solver == "naive" else 5
+    wmax = max([mult * int(e.shape[0]) for e in evecs_y] + [1])
+    payload, counts = pack_maps(mine, [wmax], per, device)
+    # concatenated-output form (world*per leading dim): accepted by both the NCCL and the gloo backend
+    all_payload = torch.empty((world * per,) + tuple(payload.shape[1:]), dtype=torch.int64, device=device)
+    all_counts = torch.empty((world * per,), dtype=torch.int64, device=device)
+    dist.all_gather_into_tensor(all_payload, payload, group=group)
+    dist.all_gather_into_tensor(all_counts, counts, group=group)
+    all_payload = all_payload.view((world, per) + tuple(payload.shape[1:]))
+    all_counts = all_counts.view(world, per)
+    out = []
+    counts_host = all_counts.cpu()
+    for r in range(world):
+        for i in range(per):
+            c = int(counts_host[r, i])
+            if c >= 0:
+                out.append(all_payload[r, i, :, :c].contiguous())
+    return out

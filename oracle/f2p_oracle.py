@@ -88,16 +88,15 @@ def _c2d(C):
 def thresholds(diam_cad) -> np.ndarray:
     """fl32(c*diam) for c in (0.3, 0.15, 0.055, 0.065) formed as torch forms them: in FP64 when `diam_cad`
     is a Python/NumPy scalar (scripts/eval.py:87 passes a list element), in FP32 when it is a 0-d FP32 tensor."""
-    cs = (0.3, 0.15, 0.055, 0.065)
-    if hasattr(diam_cad, "dtype") and hasattr(diam_cad, "detach"):  # torch tensor
-        import torch
-        if diam_cad.dtype == torch.float64:
-            d = float(diam_cad)
-            return np.array([np.float32(c * d) for c in cs], dtype=np.float32)
-        d = np.float32(diam_cad.detach().cpu().float().item())
-        return np.array([np.float32(np.float32(c) * d) for c in cs], dtype=np.float32)
-    d = float(diam_cad)
-    return np.array([np.float32(c * d) for c in cs], dtype=np.float32)
+    out = []
+    for c in (0.3, 0.15, 0.055, 0.065):
+        v = c * diam_cad
+        if hasattr(v, "detach"):
+            import torch
+            out.append(np.float32(v.detach().to(torch.float32).cpu().item()))
+        else:
+            out.append(np.float32(float(v)))
+    return np.array(out, dtype=np.float32)
 
 
 def project(evecs, C):

@@ -1,0 +1,116 @@
+"""CPU tests of the host side: the C-ABI library loads and exports every symbol include/f2p.h declares, thresholds are
+formed as torch forms them, pair sharding + all-gather works under gloo with world_size 2, and the product path
+refuses to run without CUDA (no fallback)."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    from fmap2pointmap_solvers import _lib
+    hdr = open(os.path.join(ROOT, "include", "f2p.h")).read()
+    declared = set(re.findall(r"\b(f2p_[a-z0-9_]+)\s*\(", hdr))
+    assert declared == set(_lib.exported_symbols()), declared ^ set(_lib.exported_symbols())
+    L = _lib.load()   # raises AttributeError if a declared symbol is not exported
+    assert L.f2p_version() == 100
+    assert ctypes.sizeof(_lib.F2PPairDesc) == 6 * 8 + 6 * 4 + 4 * 4
+    assert L.f2p_project_workspace_bytes() >= 256 and L.f2p_filter_workspace_bytes(1000) > 1000 * 40
+
+
+def test_no_cpu_fallback():
+    import fmap2pointmap_solvers as S
+    if torch.cuda.is_available():
+        pytest.skip("CUDA present")
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        S.naive_fmap2pointmap(torch.eye(3), torch.randn(5, 3), torch.randn(4, 3))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        S.spacial_filtering_fmap2pointmap(torch.eye(3), torch.randn(5, 3), torch.randn(4, 3), torch.rand(5, 3),
+                                          torch.rand(4, 3), 1.0)
+
+
+def test_public_api_surface():
+    import inspect
+    import fmap2pointmap_solvers as S
+    assert list(inspect.signature(S.naive_fmap2pointmap).parameters) == ["C12", "evecs_x", "evecs_y", "kwargs"]
+    assert list(inspect.signature(S.spacial_filtering_fmap2pointmap).parameters) == ["C12", "evecs_x", "evecs_y", "CAD", "PC", "diam_cad"]
+    f = lambda: None  # noqa: E731
+    assert S.choose_fmap2pointmap_solver(f) is f
+    ns = {}
+    exec("from fmap2pointmap_solvers import *", ns)
+    assert {"naive_fmap2pointmap", "spacial_filtering_fmap2pointmap", "choose_fmap2pointmap_solver"} <= set(ns)
+
+
+@pytest.mark.parametrize("diam", [17.3, np.float64(0.2345), np.float32(11.0), torch.tensor(9.7), torch.tensor(3.3, dtype=torch.float64)])
+def test_thresholds_match_torch_comparison_semantics(diam):
+    from fmap2pointmap_solvers.batched import thresholds
+    from oracle import f2p_oracle as O
+    thr = thresholds(diam)
+    np.testing.assert_array_equal(np.array(thr, np.float32), O.thresholds(diam))
+    # torch semantics: (x < c*diam) on an FP32 tensor is decided exactly at fl32 thresholds
+    for c, t in zip((0.3, 0.15, 0.055, 0.065), thr):
+        t32 = np.float32(t)
+        probe = torch.tensor([np.nextafter(t32, np.float32(-np.inf)), t32, np.nextafter(t32, np.float32(np.inf))])
+        want = (probe < c * diam).tolist()
+        assert want == [True, False, False], (c, diam, want)
+
+
+def test_shard_range_covers_everything():
+    from fmap2pointmap_solvers.distributed import shard_range
+    for n in (0, 1, 7, 8, 9, 4096):
+        for w in (1, 2, 3, 8):
+            got = []
+            for r in range(w):
+                lo, hi = shard_range(n, w, r)
+                got += list(range(lo, hi))
+            assert got == list(range(n))
+
+
+def _worker(rank, world, port, q):
+    import torch.distributed as dist
+    from fmap2pointmap_solvers.distributed import solve_sharded
+    from fmap2pointmap_solvers.synth import make_pair
+    from oracle import f2p_oracle as O
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    shapes = [(120, 40), (300, 77), (64, 64), (200, 5), (90, 130)]
+    Ps = [make_pair(a, b, 16, seed=300 + i) for i, (a, b) in enumerate(shapes)]
+
+    def compute(kind, C, ex, ey, cad, pc, diam):   # the oracle stands in for the CUDA path: this test is about sharding
+        if kind == "naive":
+            return [torch.from_numpy(O.naive(c, x, y, int16_compat=False)) for c, x, y in zip(C, ex, ey)]
+        return [torch.from_numpy(O.spatial(c, x, y, a, b, d)) for c, x, y, a, b, d in zip(C, ex, ey, cad, pc, diam)]
+
+    ok = True
+    try:
+      for kind in ("naive", "spatial"):
+        res = solve_sharded(kind, [p.C12 for p in Ps], [p.evecs_x for p in Ps], [p.evecs_y for p in Ps],
+                            [p.CAD for p in Ps], [p.PC for p in Ps], [p.diam_cad * 3 for p in Ps], compute=compute)
+        want = compute(kind, [p.C12 for p in Ps], [p.evecs_x for p in Ps], [p.evecs_y for p in Ps],
+                       [p.CAD for p in Ps], [p.PC for p in Ps], [p.diam_cad * 3 for p in Ps])
+        ok = ok and len(res) == len(want) and all(torch.equal(a, b) for a, b in zip(res, want))
+    except Exception as e:  # report instead of hanging the parent
+        import traceback
+        traceback.print_exc()
+        ok = False
+    q.put((rank, ok))
+    dist.destroy_process_group()
+
+
+def test_pair_sharding_allgather_gloo_world2():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(results) == [(0, True), (1, True)]
