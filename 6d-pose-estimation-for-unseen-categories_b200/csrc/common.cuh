@@ -98,6 +98,10 @@ __device__ __forceinline__ void unpack2(u64 v, float& lo, float& hi) {
 __device__ __forceinline__ void fma2(u64& d, u64 a, u64 b) {
     asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b));
 }
+// same, volatile: keeps the source issue order (operand-reuse pattern) through nvcc's scheduler
+__device__ __forceinline__ void fma2v(u64& d, u64 a, u64 b) {
+    asm volatile("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b));
+}
 __device__ __forceinline__ u64 add2(u64 a, u64 b) {
     u64 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r;
 }

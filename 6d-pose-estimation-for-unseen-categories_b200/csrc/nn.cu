@@ -13,6 +13,7 @@
 // The column operand (k x 128) is TMA-loaded once and stays in shared memory; the row operand arrives in
 // KC-row TMA stages through an mbarrier ring.  256 threads, each an 8x8 register tile (32 packed accumulators),
 // running (distance, index) minima live in registers across all row tiles of the CTA.
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace f2p {
@@ -47,8 +48,9 @@ __device__ __forceinline__ void insert5(u64 (&l)[5], u64 key) {
     }
 }
 
-template <int MODE>
-__global__ void __launch_bounds__(NN_THREADS, MODE == 0 ? 2 : 1)
+// MODE 0 arg-min, 1 top-5, 2 = measurement-only variant without the distance epilogue (never used by the API).
+template <int MODE, int KC, int NSTAGE>
+__global__ void __launch_bounds__(NN_THREADS, MODE == 1 ? 1 : 2)
 nn_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapY, const NNParams prm) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     const int k = prm.k;
@@ -151,12 +153,14 @@ nn_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUte
                 const ulonglong2 b0 = *reinterpret_cast<const ulonglong2*>(B + kk * TILE);
                 const ulonglong2 b1 = *reinterpret_cast<const ulonglong2*>(B + kk * TILE + 64);
                 const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+                // issue order matters on sm_100: consecutive FFMA2 sharing the PACKED (64-bit) operand hit the operand
+                // reuse cache and run at the nominal FP32 rate (74 TFLOP/s measured); sharing only the scalar
+                // broadcast operand caps at 63 TFLOP/s (profiles/r01_ffma_peak_v3.log).  Column pair outer, row inner.
+                const u64 bp[4] = {b0.x, b0.y, b1.x, b1.y};
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const u64 aa = pack2(av[i], av[i]);
-                    fma2(acc[i][0], aa, b0.x); fma2(acc[i][1], aa, b0.y);
-                    fma2(acc[i][2], aa, b1.x); fma2(acc[i][3], aa, b1.y);
-                }
+                for (int j = 0; j < 4; ++j)
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) fma2v(acc[i][j], pack2(av[i], av[i]), bp[j]);
             };
             if (klen == KC) {
 #pragma unroll
@@ -178,6 +182,7 @@ nn_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUte
             for (int jp = 0; jp < 4; ++jp) {
                 float v0, v1;
                 unpack2(add2(add2(acc[i][jp], nn), ny2[jp]), v0, v1);
+                if (MODE == 2) { bs[2 * jp] = fminf(bs[2 * jp], v0); bs[2 * jp + 1] = fminf(bs[2 * jp + 1], v1); continue; }
                 const float d0 = __fsqrt_rn(fmaxf(v0, 0.f));
                 const float d1 = __fsqrt_rn(fmaxf(v1, 0.f));
                 if (MODE == 0) {
@@ -195,7 +200,7 @@ nn_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUte
 
     // ---- cross-thread reduction: 16 threads (2 lanes x 8 warps) share each column -------------------
     __syncthreads();
-    if (MODE == 0) {
+    if (MODE != 1) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             u64 key = make_key(bs[j], bi[j]);
@@ -299,34 +304,52 @@ __global__ void fill_u64_kernel(u64* p, size_t n, u64 v) {
 }
 
 // ---- host launchers -----------------------------------------------------------------------------------
-size_t nn_smem_bytes(int k, int mode) {
-    const int nkc = (k + KC - 1) / KC;
-    size_t b = ((size_t)nkc * KC * TILE + (size_t)NSTAGE * KC * TILE) * sizeof(float) + 16 * sizeof(uint64_t);
-    b += (mode == 0 ? (size_t)8 * TILE : (size_t)8 * TILE * 5) * sizeof(u64);
+static size_t nn_smem_bytes_v(int k, int mode, int kc, int nst) {
+    const int nkc = (k + kc - 1) / kc;
+    size_t b = ((size_t)nkc * kc * TILE + (size_t)nst * kc * TILE) * sizeof(float) + 16 * sizeof(uint64_t);
+    b += (mode != 1 ? (size_t)8 * TILE : (size_t)8 * TILE * 5) * sizeof(u64);
     return b;
+}
+size_t nn_smem_bytes(int k, int mode) { return nn_smem_bytes_v(k, mode, KC, NSTAGE); }
+
+template <int MODE, int KCT, int NST>
+static int launch_variant(const float* xT, int64_t ld1_total, const float* yT, int64_t ld2_total, int k, const NNParams& prm,
+                          int total_items, cudaStream_t stream) {
+    CUtensorMap mapX, mapY;
+    int rc = make_tensor_map_2d(&mapX, xT, (uint64_t)ld1_total, (uint64_t)k, (uint64_t)ld1_total, TILE, KCT);
+    if (rc) return rc;
+    rc = make_tensor_map_2d(&mapY, yT, (uint64_t)ld2_total, (uint64_t)k, (uint64_t)ld2_total, TILE, KCT);
+    if (rc) return rc;
+    const size_t smem = nn_smem_bytes_v(k, MODE, KCT, NST);
+    F2P_CUDA(cudaFuncSetAttribute(nn_kernel<MODE, KCT, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    nn_kernel<MODE, KCT, NST><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);
+    return 0;
 }
 
 int launch_nn(int mode, const float* xT, int64_t ld1_total, const float* nx, const float* yT, int64_t ld2_total,
               const float* ny, int k, const PairDev* pairs_dev, int npairs, int uniform_items, int total_items,
               u64* best, u64* part5, cudaStream_t stream) {
     if (total_items <= 0) return 0;
-    CUtensorMap mapX, mapY;
-    int rc = make_tensor_map_2d(&mapX, xT, (uint64_t)ld1_total, (uint64_t)k, (uint64_t)ld1_total, TILE, KC);
-    if (rc) return rc;
-    rc = make_tensor_map_2d(&mapY, yT, (uint64_t)ld2_total, (uint64_t)k, (uint64_t)ld2_total, TILE, KC);
-    if (rc) return rc;
     NNParams prm;
     prm.pairs = pairs_dev; prm.npairs = npairs; prm.uniform_items = uniform_items; prm.k = k;
     prm.nx = nx; prm.ny = ny; prm.best = best; prm.part5 = part5;
-    const size_t smem = nn_smem_bytes(k, mode);
+    int rc = 0;
     if (mode == 0) {
-        F2P_CUDA(cudaFuncSetAttribute(nn_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         fill_u64_kernel<<<(unsigned)((ld2_total + 255) / 256), 256, 0, stream>>>(best, (size_t)ld2_total, ~0ull);
-        nn_kernel<0><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);
+        // F2P_NN_VARIANT: developer switch for pipeline-shape experiments (profiles/); default = 0
+        static int variant = -1;
+        if (variant < 0) { const char* e = getenv("F2P_NN_VARIANT"); variant = e ? atoi(e) : 0; }
+        switch (variant) {
+            case 1: rc = launch_variant<0, 32, 3>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream); break;
+            case 2: rc = launch_variant<0, 8, 8>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream); break;
+            case 3: rc = launch_variant<2, 16, 4>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream); break;
+            case 4: rc = launch_variant<2, 32, 3>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream); break;
+            default: rc = launch_variant<0, KC, NSTAGE>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
+        }
     } else {
-        F2P_CUDA(cudaFuncSetAttribute(nn_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        nn_kernel<1><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);
+        rc = launch_variant<1, KC, NSTAGE>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
     }
+    if (rc) return rc;
     F2P_CUDA(cudaGetLastError());
     return 0;
 }

@@ -25,11 +25,10 @@ __global__ void __launch_bounds__(256, 2) fma_peak_kernel(float* out, const floa
 #pragma unroll
             for (int u = 0; u < 4; ++u)
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const u64 aa = pack2(a[i], a[i]);
+                for (int j = 0; j < 4; ++j)   // packed operand outer: the order that reaches the nominal rate
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) asm volatile("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc[i][j]) : "l"(aa), "l"(b2[j]));
-                }
+                    for (int i = 0; i < 8; ++i)
+                        asm volatile("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc[i][j]) : "l"(pack2(a[i], a[i])), "l"(b2[j]));
         }
 #pragma unroll
         for (int i = 0; i < 8; ++i)
