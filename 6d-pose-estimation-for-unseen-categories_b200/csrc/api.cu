@@ -66,6 +66,7 @@ struct Plan {
     int uni_xtiles = 0, uni_ytiles = 0, uni_items = 0;   // >0 when every pair has the same count
     int64_t cand_total = 0;                              // sum of 5*n2
     int maxM = 0;
+    double flops = 0;                                    // 2*n1*n2*k summed over pairs
     // workspace offsets (bytes)
     size_t off_pairs = 0, off_fpairs = 0, off_xT = 0, off_nx = 0, off_yT = 0, off_ny = 0, off_keys = 0, off_cand = 0,
            off_filter = 0, total_bytes = 0;
@@ -109,6 +110,7 @@ static int build_plan(const F2PPairDesc* d, int npairs, int k, int spatial, bool
         p.cand0 = (int)P.cand_total;
         P.cand_total += 5ll * p.n2;
         if (5 * p.n2 > P.maxM) P.maxM = 5 * p.n2;
+        P.flops += 2.0 * p.n1 * (double)p.n2 * k;
     }
     auto uniform = [&](auto getter) {
         if (npairs == 0) return 0;
@@ -128,7 +130,7 @@ static int build_plan(const F2PPairDesc* d, int npairs, int k, int spatial, bool
     P.off_yT = o; o = align_up(o + sizeof(float) * (size_t)k * (size_t)P.ld2_total, 256);
     P.off_ny = o; o = align_up(o + sizeof(float) * (size_t)P.ld2_total, 256);
     P.off_keys = o;
-    o = align_up(o + (spatial ? sizeof(u64) * (size_t)P.total_items * TILE * 5 : sizeof(u64) * (size_t)P.ld2_total), 256);
+    o = align_up(o + (spatial ? sizeof(u64) * (size_t)P.total_items * TILE * 5 : argmin_ws_bytes(P.ld2_total, k, npairs)), 256);
     if (spatial) {
         P.off_cand = o;
         if (own_cand) o = align_up(o + sizeof(int64_t) * 2 * (size_t)P.cand_total, 256);
@@ -198,12 +200,11 @@ int f2p_naive_batched(const float* ex, const float* ey, const float* C, const F2
     F2P_CUDA(cudaMemcpyAsync(ws + P.off_pairs, P.pairs.data(), sizeof(PairDev) * (size_t)npairs, cudaMemcpyHostToDevice, st));
     if ((rc = run_prep(P, ex, ey, C, npairs, k, ws, st))) return rc;
     const PairDev* pd = reinterpret_cast<const PairDev*>(ws + P.off_pairs);
-    u64* best = reinterpret_cast<u64*>(ws + P.off_keys);
-    rc = launch_nn(0, reinterpret_cast<float*>(ws + P.off_xT), P.ld1_total, reinterpret_cast<float*>(ws + P.off_nx),
-                   reinterpret_cast<float*>(ws + P.off_yT), P.ld2_total, reinterpret_cast<float*>(ws + P.off_ny), k, pd,
-                   npairs, P.uni_items, P.total_items, best, nullptr, st);
-    if (rc) return rc;
-    return launch_finalize_argmin(best, pd, npairs, P.uni_ytiles, P.total_ytiles, flags, out, st);
+    ArgminWs aw;
+    argmin_ws_carve(aw, ws + P.off_keys, P.ld2_total, k, npairs);
+    return launch_argmin(reinterpret_cast<float*>(ws + P.off_xT), P.ld1_total, reinterpret_cast<float*>(ws + P.off_nx),
+                         reinterpret_cast<float*>(ws + P.off_yT), P.ld2_total, reinterpret_cast<float*>(ws + P.off_ny), k, pd,
+                         npairs, P.uni_items, P.total_items, P.uni_ytiles, P.total_ytiles, P.flops, flags, out, aw, st);
 }
 
 int f2p_spatial_batched(const float* ex, const float* ey, const float* C, const float* cad, const float* pc,
@@ -221,13 +222,12 @@ int f2p_spatial_batched(const float* ex, const float* ey, const float* C, const 
     if ((rc = run_prep(P, ex, ey, C, npairs, k, ws, st))) return rc;
     const PairDev* pd = reinterpret_cast<const PairDev*>(ws + P.off_pairs);
     u64* part5 = reinterpret_cast<u64*>(ws + P.off_keys);
-    rc = launch_nn(1, reinterpret_cast<float*>(ws + P.off_xT), P.ld1_total, reinterpret_cast<float*>(ws + P.off_nx),
-                   reinterpret_cast<float*>(ws + P.off_yT), P.ld2_total, reinterpret_cast<float*>(ws + P.off_ny), k, pd,
-                   npairs, P.uni_items, P.total_items, nullptr, part5, st);
-    if (rc) return rc;
     // candidates: caller's buffer uses the `out` layout (out_off, [2][5*n2]); the internal one is packed by cand0
     int64_t* cand = cand_dev ? cand_dev : reinterpret_cast<int64_t*>(ws + P.off_cand);
-    rc = launch_finalize_top5(part5, pd, npairs, P.uni_ytiles, P.total_ytiles, flags, cand, cand_dev != nullptr, st);
+    rc = launch_top5(reinterpret_cast<float*>(ws + P.off_xT), P.ld1_total, reinterpret_cast<float*>(ws + P.off_nx),
+                     reinterpret_cast<float*>(ws + P.off_yT), P.ld2_total, reinterpret_cast<float*>(ws + P.off_ny), k, pd,
+                     npairs, P.uni_items, P.total_items, P.uni_ytiles, P.total_ytiles, flags, part5, cand,
+                     cand_dev != nullptr, st);
     if (rc) return rc;
     return run_filter_batch(P.pairs.data(), npairs, cad, pc, cand, cand_dev != nullptr, out, counts, status,
                             ws + P.off_fpairs, ws, P.filter_off.data(), st);

@@ -51,12 +51,11 @@ int f2p_project(const float* evecs, int n, int k, int ld_in, const float* C, flo
 }
 
 size_t f2p_nn_workspace_bytes(int n1, int n2, int k, int top5) {
-    (void)k;
     const int nrt = (n1 + TILE - 1) / TILE, nct = (n2 + TILE - 1) / TILE;
     const int ns = pick_nsplit(nrt, nct);
     size_t b = 256;
     if (top5) b += sizeof(unsigned long long) * (size_t)nct * ns * TILE * 5;
-    else b += sizeof(unsigned long long) * (size_t)nct * TILE;
+    else b += argmin_ws_bytes((int64_t)nct * TILE, k, 1);
     return (b + 255) & ~(size_t)255;
 }
 
@@ -72,23 +71,23 @@ static int nn_common(int mode, const float* xT, const float* nx, int n1, int ld1
     const int nrt = (n1 + TILE - 1) / TILE, nct = (n2 + TILE - 1) / TILE;
     int rc = single_pair(p, n1, n2, ld1, ld2, pick_nsplit(nrt, nct));
     if (rc) return rc;
+    if (mode == 0 && ld2 != nct * TILE) {
+        set_error("f2p_nn_argmin needs ld2 == round_up(n2, %d) (the re-check operand shares the layout)", TILE);
+        return F2P_EINVAL;
+    }
     unsigned char* ws = static_cast<unsigned char*>(ws_v);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     F2P_CUDA(cudaMemcpyAsync(ws, &p, sizeof(p), cudaMemcpyHostToDevice, st));
     const PairDev* pd = reinterpret_cast<const PairDev*>(ws);
-    unsigned long long* keys = reinterpret_cast<unsigned long long*>(ws + 256);
     const int items = p.nct * p.nsplit;
-    // the single-op layout is the batch layout with one pair: ld*_total = ld*, but `best` is indexed by column
     if (mode == 0) {
-        if ((size_t)ld2 > (size_t)nct * TILE) { /* best[] sized by nct*TILE: columns beyond are never touched */ }
-        rc = launch_nn(0, xT, ld1, nx, yT, ld2, ny, k, pd, 1, items, items, keys, nullptr, st);
-        if (rc) return rc;
-        // out: int64 [n2] only (row 0); reuse the batch finaliser into a temporary [2,n2]?  No: write row 0 in place.
-        return launch_finalize_argmin(keys, pd, 1, p.nct, p.nct, F2P_ROW0_ONLY, out, st);
+        ArgminWs aw;
+        argmin_ws_carve(aw, ws + 256, ld2, k, 1);
+        return launch_argmin(xT, ld1, nx, yT, ld2, ny, k, pd, 1, items, items, p.nct, p.nct, 2.0 * n1 * (double)n2 * k,
+                             F2P_ROW0_ONLY, out, aw, st);
     }
-    rc = launch_nn(1, xT, ld1, nx, yT, ld2, ny, k, pd, 1, items, items, nullptr, keys, st);
-    if (rc) return rc;
-    return launch_finalize_top5(keys, pd, 1, p.nct, p.nct, F2P_ROW0_ONLY, out, 1, st);
+    return launch_top5(xT, ld1, nx, yT, ld2, ny, k, pd, 1, items, items, p.nct, p.nct, F2P_ROW0_ONLY,
+                       reinterpret_cast<unsigned long long*>(ws + 256), out, 1, st);
 }
 
 int f2p_nn_argmin(const float* xT, const float* nx, int n1, int ld1, const float* yT, const float* ny, int n2, int ld2,

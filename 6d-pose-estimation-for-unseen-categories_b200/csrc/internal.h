@@ -24,14 +24,21 @@ int launch_project(bool is_x, const float* evecs, const float* Cmat, const PairD
                    int uniform_tiles, int total_tiles, int k, float* outT, int64_t ld_total, float* nrm,
                    cudaStream_t stream);
 // nn.cu
+struct ArgminWs {
+    unsigned long long* best; unsigned long long* best_exact; float* yTf; float* nyf;
+    uint32_t* best2; int* flagged; int* nflag;
+};
 size_t nn_smem_bytes(int k, int mode);
-int launch_nn(int mode, const float* xT, int64_t ld1_total, const float* nx, const float* yT, int64_t ld2_total,
-              const float* ny, int k, const PairDev* pairs_dev, int npairs, int uniform_items, int total_items,
-              unsigned long long* best, unsigned long long* part5, cudaStream_t stream);
-int launch_finalize_argmin(const unsigned long long* best, const PairDev* pairs_dev, int npairs, int uniform_tiles,
-                           int total_ytiles, unsigned flags, int64_t* out, cudaStream_t stream);
-int launch_finalize_top5(const unsigned long long* part5, const PairDev* pairs_dev, int npairs, int uniform_tiles,
-                         int total_ytiles, unsigned flags, int64_t* cand, int cand_is_out_layout, cudaStream_t stream);
+size_t argmin_ws_bytes(int64_t ld2_total, int k, int npairs);
+void argmin_ws_carve(ArgminWs& w, unsigned char* base, int64_t ld2_total, int k, int npairs);
+int launch_argmin(const float* xT, int64_t ld1_total, const float* nx, const float* yT, int64_t ld2_total,
+                  const float* ny, int k, const PairDev* pairs_dev, int npairs, int uniform_items, int total_items,
+                  int uniform_ytiles, int total_ytiles, double flops, unsigned flags, int64_t* out, const ArgminWs& w,
+                  cudaStream_t stream);
+int launch_top5(const float* xT, int64_t ld1_total, const float* nx, const float* yT, int64_t ld2_total, const float* ny,
+                int k, const PairDev* pairs_dev, int npairs, int uniform_items, int total_items, int uniform_ytiles,
+                int total_ytiles, unsigned flags, unsigned long long* part5, int64_t* cand, int cand_is_out_layout,
+                cudaStream_t stream);
 // filter.cu
 size_t filter_pair_bytes(int M);
 size_t filter_table_bytes(int npairs);

@@ -15,6 +15,7 @@
 // running (distance, index) minima live in registers across all row tiles of the CTA.
 #include <stdlib.h>
 #include "common.cuh"
+#include "internal.h"
 
 namespace f2p {
 
@@ -25,11 +26,14 @@ struct NNParams {
     int k;
     const float* nx;     // [ld1_total] row norms (+inf on padding)
     const float* ny;     // [ld2_total] column norms
-    u64* best;           // MODE 0: [ld2_total] packed (d bits << 32 | i) keys, pre-set to ~0
+    u64* best;           // MODE 0/2: [ld2_total] packed (value bits << 32 | i) keys, pre-set to ~0
     u64* part5;          // MODE 1: [total_items][TILE][5] keys
+    uint32_t* best2;     // MODE 2: [ld2_total] bits of the second-smallest clamped d2 per column, pre-set to +inf bits
+    const int* ncols;    // MODE 0 re-check pass: per-pair number of (compacted) columns to process, or null = n2
 };
 
 constexpr uint32_t IDX_NONE = 0x7fffffffu;
+constexpr int PRODUCER_TID = NN_THREADS - 32;   // lane 0 of the last (highest-priority) warp issues all TMA loads
 
 __device__ __forceinline__ u64 make_key(float d, uint32_t i) {
     return ((u64)(__float_as_uint(d) & 0x7fffffffu) << 32) | (u64)i;
@@ -48,7 +52,11 @@ __device__ __forceinline__ void insert5(u64 (&l)[5], u64 key) {
     }
 }
 
-// MODE 0 arg-min, 1 top-5, 2 = measurement-only variant without the distance epilogue (never used by the API).
+// MODE 0: exact arg-min (sqrt_rn per element, reference semantics by construction).
+// MODE 1: exact top-5 ordered by (distance, index).
+// MODE 2: raw first pass of the two-phase arg-min: tracks the smallest clamped d2 with its row and the second-smallest
+//         value per column, no square roots.  Columns whose two smallest d2 fall into the same sqrt_rn class are
+//         re-checked by a MODE 0 pass over the compacted list of those columns (finalize_raw_kernel decides).
 template <int MODE, int KC, int NSTAGE>
 __global__ void __launch_bounds__(NN_THREADS, MODE == 1 ? 1 : 2)
 nn_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapY, const NNParams prm) {
@@ -64,12 +72,17 @@ nn_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUte
     u64* red = reinterpret_cast<u64*>(bars + 16);                    // MODE 0: [8][TILE]; MODE 1: [8][TILE][5]
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tx = tid & 15, ty = tid >> 4;
+    // Thread -> (ty, tx) of the 16x16 grid of 8x8 register tiles.  Shared memory serves LDS.128 per HALF-warp, one
+    // wavefront per 128 distinct bytes: a half-warp laid out 2 (rows) x 8 (columns) reads 32 B of the row operand and
+    // 128 B of the column operand per load = 1 wavefront each (8 per warp k-step instead of 12 for a 1 x 16 layout).
+    const int tx = ((warp & 1) << 3) | (lane & 7);
+    const int ty = ((warp >> 1) << 2) | ((lane >> 4) << 1) | ((lane >> 3) & 1);
 
     const int item = blockIdx.x;
     const int pi = find_pair(item, prm.pairs, prm.npairs, prm.uniform_items, &PairDev::item0);
     const PairDev* pdp = prm.pairs + pi;
-    const int pd_nsplit = pdp->nsplit, pd_nrt = pdp->nrt, pd_n2 = pdp->n2;
+    const int pd_nsplit = pdp->nsplit, pd_nrt = pdp->nrt;
+    const int pd_n2 = (MODE == 0 && prm.ncols) ? prm.ncols[pi] : pdp->n2;
     const int local = item - pdp->item0;
     const int ct = local / pd_nsplit, sp = local - ct * pd_nsplit;
     const int t_begin = (int)(((long long)sp * pd_nrt) / pd_nsplit);
@@ -77,6 +90,7 @@ nn_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUte
     const int ntiles = t_end - t_begin;
     const int xcol = pdp->x_col0, ycol = pdp->y_col0 + ct * TILE;
     const int total_stages = ntiles * nkc;
+    if (ct * TILE >= pd_n2) return;   // re-check pass: fewer compacted columns than the grid was sized for (uniform exit)
 
     if (tid == 0) {
         tma_prefetch_desc(&mapX);
@@ -92,7 +106,7 @@ nn_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUte
         mbar_arrive_expect_tx(&full[slot], KC * TILE * sizeof(float));
         tma_load_2d(sA + (size_t)slot * KC * TILE, &mapX, xcol + (t_begin + t) * TILE, kc * KC, &full[slot]);
     };
-    if (tid == 0) {
+    if (tid == PRODUCER_TID) {
         mbar_arrive_expect_tx(fullB, (uint32_t)(nkc * KC * TILE * sizeof(float)));
         for (int kc = 0; kc < nkc; ++kc) tma_load_2d(sB + (size_t)kc * KC * TILE, &mapY, ycol, kc * KC, fullB);
         for (int s = 0; s < NSTAGE && s < total_stages; ++s) issue(s);
@@ -108,11 +122,12 @@ nn_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUte
     }
 
     // running minima
-    float bs[8]; uint32_t bi[8];          // MODE 0
+    float bs[8]; uint32_t bi[8];          // MODE 0: best distance / row; MODE 2: smallest clamped d2 / row
+    float b2[MODE == 2 ? 8 : 1];          // MODE 2: second-smallest clamped d2
     u64 l5[MODE == 1 ? 8 : 1][5];         // MODE 1
     const float INF = __int_as_float(0x7f800000);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { bs[j] = INF; bi[j] = IDX_NONE; }
+    for (int j = 0; j < 8; ++j) { bs[j] = INF; bi[j] = IDX_NONE; b2[MODE == 2 ? j : 0] = INF; }
     if (MODE == 1) {
 #pragma unroll
         for (int j = 0; j < 8; ++j)
@@ -136,7 +151,10 @@ nn_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUte
         for (int kc = 0; kc < nkc; ++kc, ++s) {
             const int slot = s % NSTAGE;
             const uint32_t ph = (uint32_t)((s / NSTAGE) & 1);
-            if (tid == 0 && s >= 1) {
+            // The refilling thread must belong to the warp that runs AHEAD: the SM's warp arbiter favours the highest
+            // warp id, so a low-id producer lags and the leading warps find their stage not even requested yet
+            // (ncu: 8.4 % of samples parked on the full barrier with thread 0 as producer).
+            if (tid == PRODUCER_TID && s >= 1) {
                 const int sn = s - 1 + NSTAGE;
                 if (sn < total_stages) {
                     mbar_wait(&empty[(s - 1) % NSTAGE], (uint32_t)(((s - 1) / NSTAGE) & 1));
@@ -182,7 +200,16 @@ nn_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUte
             for (int jp = 0; jp < 4; ++jp) {
                 float v0, v1;
                 unpack2(add2(add2(acc[i][jp], nn), ny2[jp]), v0, v1);
-                if (MODE == 2) { bs[2 * jp] = fminf(bs[2 * jp], v0); bs[2 * jp + 1] = fminf(bs[2 * jp + 1], v1); continue; }
+                if (MODE == 2) {
+                    const float c0 = fmaxf(v0, 0.f), c1 = fmaxf(v1, 0.f);
+                    const int ja = 2 * jp, jb = 2 * jp + 1;
+                    b2[MODE == 2 ? ja : 0] = fminf(b2[MODE == 2 ? ja : 0], fmaxf(c0, bs[ja]));
+                    b2[MODE == 2 ? jb : 0] = fminf(b2[MODE == 2 ? jb : 0], fmaxf(c1, bs[jb]));
+                    const bool p0 = c0 < bs[ja], p1 = c1 < bs[jb];
+                    bs[ja] = fminf(bs[ja], c0); bi[ja] = p0 ? row : bi[ja];
+                    bs[jb] = fminf(bs[jb], c1); bi[jb] = p1 ? row : bi[jb];
+                    continue;
+                }
                 const float d0 = __fsqrt_rn(fmaxf(v0, 0.f));
                 const float d1 = __fsqrt_rn(fmaxf(v1, 0.f));
                 if (MODE == 0) {
@@ -198,39 +225,82 @@ nn_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUte
         }
     }
 
-    // ---- cross-thread reduction: 16 threads (2 lanes x 8 warps) share each column -------------------
+    // ---- cross-thread reduction: the 16 threads sharing a column are 4 lanes (xor 8, xor 16) x 4 warps --------
     __syncthreads();
-    if (MODE != 1) {
+    const int wrow = warp >> 1;   // 0..3: which 4-ty band this warp covers
+    if (MODE == 2) {
+        float* red2 = reinterpret_cast<float*>(red + 4 * TILE);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             u64 key = make_key(bs[j], bi[j]);
-            const u64 o = shfl_xor_u64(key, 16);
+            float sec = b2[MODE == 2 ? j : 0];
+#pragma unroll
+            for (int m = 8; m <= 16; m <<= 1) {
+                const u64 ok = shfl_xor_u64(key, m);
+                const float os = __shfl_xor_sync(0xffffffffu, sec, m);
+                // second smallest of the union: the smaller "second" or the larger of the two minima
+                sec = fminf(fminf(sec, os), fmaxf(__uint_as_float((uint32_t)(key >> 32)), __uint_as_float((uint32_t)(ok >> 32))));
+                key = ok < key ? ok : key;
+            }
+            const int col = (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
+            if (lane < 8) { red[wrow * TILE + col] = key; red2[wrow * TILE + col] = sec; }
+        }
+        __syncthreads();
+        if (tid < TILE) {
+            u64 key = red[tid];
+            float sec = red2[tid];
+#pragma unroll
+            for (int w = 1; w < 4; ++w) {
+                const u64 ok = red[w * TILE + tid];
+                sec = fminf(fminf(sec, red2[w * TILE + tid]),
+                            fmaxf(__uint_as_float((uint32_t)(key >> 32)), __uint_as_float((uint32_t)(ok >> 32))));
+                key = ok < key ? ok : key;
+            }
+            if (ct * TILE + tid < pd_n2) {
+                // cross-CTA merge: the loser of every atomicMin exchange (incoming or displaced) feeds `best2`
+                const u64 old = atomicMin(prm.best + ycol + tid, key);
+                uint32_t loser = (uint32_t)((old < key ? key : old) >> 32);   // old == ~0: 0xffffffff, ignored by min
+                const uint32_t secb = __float_as_uint(sec);
+                loser = loser < secb ? loser : secb;
+                atomicMin(prm.best2 + ycol + tid, loser);
+            }
+        }
+    } else if (MODE == 0) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            u64 key = make_key(bs[j], bi[j]);
+            u64 o = shfl_xor_u64(key, 8);
+            key = o < key ? o : key;
+            o = shfl_xor_u64(key, 16);
             key = o < key ? o : key;
             const int col = (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
-            if (lane < 16) red[warp * TILE + col] = key;
+            if (lane < 8) red[wrow * TILE + col] = key;
         }
         __syncthreads();
         if (tid < TILE) {
             u64 m = red[tid];
 #pragma unroll
-            for (int w = 1; w < 8; ++w) { const u64 o = red[w * TILE + tid]; m = o < m ? o : m; }
+            for (int w = 1; w < 4; ++w) { const u64 o = red[w * TILE + tid]; m = o < m ? o : m; }
             if (ct * TILE + tid < pd_n2) atomicMin(prm.best + ycol + tid, m);
         }
     } else {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            u64 mine[5];
+            u64 mine[5], other[5];
 #pragma unroll
             for (int r = 0; r < 5; ++r) mine[r] = l5[MODE == 1 ? j : 0][r];
 #pragma unroll
-            for (int r = 0; r < 5; ++r) {
-                const u64 o = shfl_xor_u64(l5[MODE == 1 ? j : 0][r], 16);
-                insert5(mine, o);
-            }
-            const int col = (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
-            if (lane < 16) {
+            for (int r = 0; r < 5; ++r) other[r] = shfl_xor_u64(mine[r], 8);
 #pragma unroll
-                for (int r = 0; r < 5; ++r) red[((size_t)warp * TILE + col) * 5 + r] = mine[r];
+            for (int r = 0; r < 5; ++r) insert5(mine, other[r]);
+#pragma unroll
+            for (int r = 0; r < 5; ++r) other[r] = shfl_xor_u64(mine[r], 16);
+#pragma unroll
+            for (int r = 0; r < 5; ++r) insert5(mine, other[r]);
+            const int col = (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
+            if (lane < 8) {
+#pragma unroll
+                for (int r = 0; r < 5; ++r) red[((size_t)wrow * TILE + col) * 5 + r] = mine[r];
             }
         }
         __syncthreads();
@@ -238,7 +308,7 @@ nn_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUte
             u64 m[5];
 #pragma unroll
             for (int r = 0; r < 5; ++r) m[r] = red[(size_t)tid * 5 + r];
-            for (int w = 1; w < 8; ++w)
+            for (int w = 1; w < 4; ++w)
 #pragma unroll
                 for (int r = 0; r < 5; ++r) insert5(m, red[((size_t)w * TILE + tid) * 5 + r]);
 #pragma unroll
@@ -298,74 +368,179 @@ finalize_top5_kernel(const u64* __restrict__ part5, const PairDev* __restrict__ 
     }
 }
 
-__global__ void fill_u64_kernel(u64* p, size_t n, u64 v) {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) p[i] = v;
+// ---- two-phase arg-min support kernels ----------------------------------------------------------------
+// Initialises the per-column merge state of an arg-min pass (and the per-pair re-check counters).
+__global__ void argmin_init_kernel(u64* best, uint32_t* best2, u64* best_exact, size_t n, int* nflag, int npairs) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        best[i] = ~0ull;
+        if (best2) best2[i] = 0x7f800000u;
+        if (best_exact) best_exact[i] = ~0ull;
+    }
+    if (nflag && i < (size_t)npairs) nflag[i] = 0;
+}
+
+// After the raw pass: a column is decided when its two smallest clamped d2 round to different sqrt_rn values
+// (sqrt is monotone, so every other row is farther).  Otherwise exact ties in distance are possible and the lowest
+// index among them may not be the raw minimum: the column joins the pair's re-check list.  Also writes row 1.
+__global__ void __launch_bounds__(TILE)
+finalize_raw_kernel(const u64* __restrict__ best, const uint32_t* __restrict__ best2, const PairDev* __restrict__ pairs,
+                    int npairs, int uniform_tiles, unsigned flags, int64_t* __restrict__ out, int* __restrict__ nflag,
+                    int* __restrict__ flagged) {
+    const int pi = find_pair(blockIdx.x, pairs, npairs, uniform_tiles, &PairDev::ytile0);
+    const PairDev* pd = pairs + pi;
+    const int j = (blockIdx.x - pd->ytile0) * TILE + threadIdx.x;
+    const int n2 = pd->n2;
+    if (j >= n2) return;
+    const u64 key = best[pd->y_col0 + j];
+    uint32_t idx = (uint32_t)(key & 0xffffffffull);
+    const float m1 = __uint_as_float((uint32_t)(key >> 32));
+    const float m2 = __uint_as_float(best2[pd->y_col0 + j]);
+    int64_t* o = out + pd->out_off;
+    if (!(flags & F2P_ROW0_ONLY)) o[(int64_t)n2 + j] = row1_value(j, flags);
+    if (idx == IDX_NONE) { o[j] = 0; return; }              // all distances +inf/NaN: out of contract
+    if (__fsqrt_rn(m2) == __fsqrt_rn(m1)) {                  // possible exact tie after the square root
+        const int f = atomicAdd(nflag + pi, 1);
+        flagged[pd->y_col0 + f] = j;
+    } else {
+        o[j] = (int64_t)idx;
+    }
+}
+
+// Compacts the flagged columns of every pair into the re-check operand (same k-major layout as yT).
+__global__ void __launch_bounds__(TILE)
+gather_flagged_kernel(const float* __restrict__ yT, const float* __restrict__ ny, const PairDev* __restrict__ pairs,
+                      int npairs, int uniform_tiles, int k, int64_t ld2_total, const int* __restrict__ nflag,
+                      const int* __restrict__ flagged, float* __restrict__ yTf, float* __restrict__ nyf) {
+    const int pi = find_pair(blockIdx.x, pairs, npairs, uniform_tiles, &PairDev::ytile0);
+    const PairDev* pd = pairs + pi;
+    const int f = (blockIdx.x - pd->ytile0) * TILE + threadIdx.x;
+    const int nf = nflag[pi];
+    if ((blockIdx.x - pd->ytile0) * TILE >= nf) return;
+    const int64_t dst = (int64_t)pd->y_col0 + f;
+    if (f < nf) {
+        const int64_t src = (int64_t)pd->y_col0 + flagged[pd->y_col0 + f];
+        for (int c = 0; c < k; ++c) yTf[(int64_t)c * ld2_total + dst] = yT[(int64_t)c * ld2_total + src];
+        nyf[dst] = ny[src];
+    } else {   // tail of the last compacted tile: defined values, results are never read back
+        for (int c = 0; c < k; ++c) yTf[(int64_t)c * ld2_total + dst] = 0.f;
+        nyf[dst] = 0.f;
+    }
+}
+
+__global__ void __launch_bounds__(TILE)
+finalize_recheck_kernel(const u64* __restrict__ best_exact, const PairDev* __restrict__ pairs, int npairs,
+                        int uniform_tiles, const int* __restrict__ nflag, const int* __restrict__ flagged,
+                        int64_t* __restrict__ out) {
+    const int pi = find_pair(blockIdx.x, pairs, npairs, uniform_tiles, &PairDev::ytile0);
+    const PairDev* pd = pairs + pi;
+    const int f = (blockIdx.x - pd->ytile0) * TILE + threadIdx.x;
+    if (f >= nflag[pi]) return;
+    const int j = flagged[pd->y_col0 + f];
+    out[pd->out_off + j] = (int64_t)(uint32_t)(best_exact[pd->y_col0 + f] & 0xffffffffull);
 }
 
 // ---- host launchers -----------------------------------------------------------------------------------
 static size_t nn_smem_bytes_v(int k, int mode, int kc, int nst) {
     const int nkc = (k + kc - 1) / kc;
     size_t b = ((size_t)nkc * kc * TILE + (size_t)nst * kc * TILE) * sizeof(float) + 16 * sizeof(uint64_t);
-    b += (mode != 1 ? (size_t)8 * TILE : (size_t)8 * TILE * 5) * sizeof(u64);
+    b += (mode != 1 ? (size_t)8 * TILE : (size_t)4 * TILE * 5) * sizeof(u64);
     return b;
 }
 size_t nn_smem_bytes(int k, int mode) { return nn_smem_bytes_v(k, mode, KC, NSTAGE); }
 
-template <int MODE, int KCT, int NST>
-static int launch_variant(const float* xT, int64_t ld1_total, const float* yT, int64_t ld2_total, int k, const NNParams& prm,
-                          int total_items, cudaStream_t stream) {
+template <int MODE>
+static int launch_mode(const float* xT, int64_t ld1_total, const float* yT, int64_t ld2_total, int k, const NNParams& prm,
+                       int total_items, cudaStream_t stream) {
     CUtensorMap mapX, mapY;
-    int rc = make_tensor_map_2d(&mapX, xT, (uint64_t)ld1_total, (uint64_t)k, (uint64_t)ld1_total, TILE, KCT);
+    int rc = make_tensor_map_2d(&mapX, xT, (uint64_t)ld1_total, (uint64_t)k, (uint64_t)ld1_total, TILE, KC);
     if (rc) return rc;
-    rc = make_tensor_map_2d(&mapY, yT, (uint64_t)ld2_total, (uint64_t)k, (uint64_t)ld2_total, TILE, KCT);
+    rc = make_tensor_map_2d(&mapY, yT, (uint64_t)ld2_total, (uint64_t)k, (uint64_t)ld2_total, TILE, KC);
     if (rc) return rc;
-    const size_t smem = nn_smem_bytes_v(k, MODE, KCT, NST);
-    F2P_CUDA(cudaFuncSetAttribute(nn_kernel<MODE, KCT, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    nn_kernel<MODE, KCT, NST><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);
+    const size_t smem = nn_smem_bytes_v(k, MODE, KC, NSTAGE);
+    F2P_CUDA(cudaFuncSetAttribute(nn_kernel<MODE, KC, NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    nn_kernel<MODE, KC, NSTAGE><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);
+    F2P_CUDA(cudaGetLastError());
     return 0;
 }
 
-int launch_nn(int mode, const float* xT, int64_t ld1_total, const float* nx, const float* yT, int64_t ld2_total,
-              const float* ny, int k, const PairDev* pairs_dev, int npairs, int uniform_items, int total_items,
-              u64* best, u64* part5, cudaStream_t stream) {
-    if (total_items <= 0) return 0;
+size_t argmin_ws_bytes(int64_t ld2_total, int k, int npairs) {
+    const size_t n = (size_t)ld2_total;
+    size_t b = 0;
+    b += n * sizeof(u64);                       // best
+    b += n * sizeof(uint32_t);                  // best2
+    b += n * sizeof(u64);                       // best_exact
+    b += n * sizeof(int);                       // flagged
+    b += n * sizeof(float);                     // nyf
+    b += ((size_t)(npairs > 0 ? npairs : 1) * sizeof(int) + 255) & ~(size_t)255;   // nflag
+    b += (size_t)k * n * sizeof(float);         // yTf
+    return (b + 255) & ~(size_t)255;
+}
+
+void argmin_ws_carve(ArgminWs& w, unsigned char* base, int64_t ld2_total, int k, int npairs) {
+    const size_t n = (size_t)ld2_total;
+    unsigned char* p = base;
+    w.best = reinterpret_cast<u64*>(p); p += n * sizeof(u64);
+    w.best_exact = reinterpret_cast<u64*>(p); p += n * sizeof(u64);
+    w.yTf = reinterpret_cast<float*>(p); p += (size_t)k * n * sizeof(float);
+    w.nyf = reinterpret_cast<float*>(p); p += n * sizeof(float);
+    w.best2 = reinterpret_cast<uint32_t*>(p); p += n * sizeof(uint32_t);
+    w.flagged = reinterpret_cast<int*>(p); p += n * sizeof(int);
+    w.nflag = reinterpret_cast<int*>(p);
+}
+
+// Two-phase threshold: below this much arithmetic the extra launches of the re-check path cost more than the
+// square roots they save, so the exact kernel runs directly.
+static bool use_two_phase(double flops) {
+    const char* e = getenv("F2P_ARGMIN_TWO_PHASE");   // test/override switch: "0" exact pass only, "1" always two-phase
+    if (e && (e[0] == '0' || e[0] == '1')) return e[0] == '1';
+    return flops >= 5e9;
+}
+
+int launch_argmin(const float* xT, int64_t ld1_total, const float* nx, const float* yT, int64_t ld2_total,
+                  const float* ny, int k, const PairDev* pairs_dev, int npairs, int uniform_items, int total_items,
+                  int uniform_ytiles, int total_ytiles, double flops, unsigned flags, int64_t* out, const ArgminWs& w,
+                  cudaStream_t stream) {
+    if (total_items <= 0 || total_ytiles <= 0) return 0;
     NNParams prm;
     prm.pairs = pairs_dev; prm.npairs = npairs; prm.uniform_items = uniform_items; prm.k = k;
-    prm.nx = nx; prm.ny = ny; prm.best = best; prm.part5 = part5;
-    int rc = 0;
-    if (mode == 0) {
-        fill_u64_kernel<<<(unsigned)((ld2_total + 255) / 256), 256, 0, stream>>>(best, (size_t)ld2_total, ~0ull);
-        // F2P_NN_VARIANT: developer switch for pipeline-shape experiments (profiles/); default = 0
-        static int variant = -1;
-        if (variant < 0) { const char* e = getenv("F2P_NN_VARIANT"); variant = e ? atoi(e) : 0; }
-        switch (variant) {
-            case 1: rc = launch_variant<0, 32, 3>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream); break;
-            case 2: rc = launch_variant<0, 8, 8>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream); break;
-            case 3: rc = launch_variant<2, 16, 4>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream); break;
-            case 4: rc = launch_variant<2, 32, 3>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream); break;
-            default: rc = launch_variant<0, KC, NSTAGE>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
-        }
-    } else {
-        rc = launch_variant<1, KC, NSTAGE>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
+    prm.nx = nx; prm.ny = ny; prm.best = w.best; prm.part5 = nullptr; prm.best2 = nullptr; prm.ncols = nullptr;
+    const bool two = use_two_phase(flops);
+    const unsigned iblocks = (unsigned)((ld2_total + 255) / 256);
+    int rc;
+    if (!two) {
+        argmin_init_kernel<<<iblocks, 256, 0, stream>>>(w.best, nullptr, nullptr, (size_t)ld2_total, nullptr, 0);
+        if ((rc = launch_mode<0>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream))) return rc;
+        finalize_argmin_kernel<<<total_ytiles, TILE, 0, stream>>>(w.best, pairs_dev, npairs, uniform_ytiles, flags, out);
+        F2P_CUDA(cudaGetLastError());
+        return 0;
     }
+    argmin_init_kernel<<<iblocks, 256, 0, stream>>>(w.best, w.best2, w.best_exact, (size_t)ld2_total, w.nflag, npairs);
+    prm.best2 = w.best2;
+    if ((rc = launch_mode<2>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream))) return rc;
+    finalize_raw_kernel<<<total_ytiles, TILE, 0, stream>>>(w.best, w.best2, pairs_dev, npairs, uniform_ytiles, flags, out,
+                                                          w.nflag, w.flagged);
+    gather_flagged_kernel<<<total_ytiles, TILE, 0, stream>>>(yT, ny, pairs_dev, npairs, uniform_ytiles, k, ld2_total,
+                                                            w.nflag, w.flagged, w.yTf, w.nyf);
+    // exact re-check over the compacted columns: the grid is sized for the worst case, surplus CTAs exit at once
+    prm.best = w.best_exact; prm.best2 = nullptr; prm.ny = w.nyf; prm.ncols = w.nflag;
+    if ((rc = launch_mode<0>(xT, ld1_total, w.yTf, ld2_total, k, prm, total_items, stream))) return rc;
+    finalize_recheck_kernel<<<total_ytiles, TILE, 0, stream>>>(w.best_exact, pairs_dev, npairs, uniform_ytiles, w.nflag,
+                                                              w.flagged, out);
+    F2P_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int launch_top5(const float* xT, int64_t ld1_total, const float* nx, const float* yT, int64_t ld2_total, const float* ny,
+                int k, const PairDev* pairs_dev, int npairs, int uniform_items, int total_items, int uniform_ytiles,
+                int total_ytiles, unsigned flags, u64* part5, int64_t* cand, int cand_is_out_layout, cudaStream_t stream) {
+    if (total_items <= 0 || total_ytiles <= 0) return 0;
+    NNParams prm;
+    prm.pairs = pairs_dev; prm.npairs = npairs; prm.uniform_items = uniform_items; prm.k = k;
+    prm.nx = nx; prm.ny = ny; prm.best = nullptr; prm.part5 = part5; prm.best2 = nullptr; prm.ncols = nullptr;
+    int rc = launch_mode<1>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
     if (rc) return rc;
-    F2P_CUDA(cudaGetLastError());
-    return 0;
-}
-
-int launch_finalize_argmin(const u64* best, const PairDev* pairs_dev, int npairs, int uniform_tiles, int total_ytiles,
-                           unsigned flags, int64_t* out, cudaStream_t stream) {
-    if (total_ytiles <= 0) return 0;
-    finalize_argmin_kernel<<<total_ytiles, TILE, 0, stream>>>(best, pairs_dev, npairs, uniform_tiles, flags, out);
-    F2P_CUDA(cudaGetLastError());
-    return 0;
-}
-
-int launch_finalize_top5(const u64* part5, const PairDev* pairs_dev, int npairs, int uniform_tiles, int total_ytiles,
-                         unsigned flags, int64_t* cand, int cand_is_out_layout, cudaStream_t stream) {
-    if (total_ytiles <= 0) return 0;
-    finalize_top5_kernel<<<total_ytiles, TILE, 0, stream>>>(part5, pairs_dev, npairs, uniform_tiles, flags, cand, cand_is_out_layout);
+    finalize_top5_kernel<<<total_ytiles, TILE, 0, stream>>>(part5, pairs_dev, npairs, uniform_ytiles, flags, cand, cand_is_out_layout);
     F2P_CUDA(cudaGetLastError());
     return 0;
 }

@@ -32,13 +32,20 @@ def oracle():
     return O
 
 
+@pytest.fixture(params=["exact", "two_phase"])
+def argmin_path(request, monkeypatch):
+    """Runs a test through both arg-min paths: the exact kernel alone and raw pass + re-check of ambiguous columns."""
+    monkeypatch.setenv("F2P_ARGMIN_TWO_PHASE", "1" if request.param == "two_phase" else "0")
+    return request.param
+
+
 def _cuda(inp):
     return {k: (v.cuda() if isinstance(v, torch.Tensor) and k != "diam_cad" else v) for k, v in inp.items()}
 
 
 # ---------------------------------------------------------------------------------------------- naive
 @pytest.mark.parametrize("name", NAIVE)
-def test_naive_matches_reference_golden(solvers, golden, name):
+def test_naive_matches_reference_golden(solvers, golden, name, argmin_path):
     c, inp = load_case(golden, name)
     d = _cuda(inp)
     got = solvers.naive_fmap2pointmap(d["C12"], d["evecs_x"], d["evecs_y"], int16_compat=True)
@@ -77,7 +84,7 @@ def test_naive_requires_grad_and_noncontiguous(solvers, oracle):
 
 @pytest.mark.parametrize("shape", [(1, 1, 1), (5, 1, 3), (127, 129, 17), (128, 128, 16), (129, 127, 15),
                                    (1000, 3, 50), (3, 1000, 50), (777, 555, 100), (2500, 300, 256)])
-def test_naive_edge_shapes_vs_oracle(solvers, oracle, shape):
+def test_naive_edge_shapes_vs_oracle(solvers, oracle, shape, argmin_path):
     from fmap2pointmap_solvers.synth import make_pair
     n1, n2, k = shape
     P = make_pair(n1, n2, k, seed=500 + n1 + n2 + k)
@@ -94,7 +101,7 @@ def test_naive_errors(solvers):
     assert tuple(out.shape) == (2, 0) and out.dtype == torch.int64
 
 
-def test_naive_batched_ragged(solvers, oracle):
+def test_naive_batched_ragged(solvers, oracle, argmin_path):
     from fmap2pointmap_solvers.synth import make_pair
     shapes = [(300, 200), (1000, 64), (129, 500), (5, 5), (2048, 1024)]
     Ps = [make_pair(a, b, 30, seed=40 + i) for i, (a, b) in enumerate(shapes)]
