@@ -130,7 +130,7 @@ static int build_plan(const F2PPairDesc* d, int npairs, int k, int spatial, bool
     P.off_yT = o; o = align_up(o + sizeof(float) * (size_t)k * (size_t)P.ld2_total, 256);
     P.off_ny = o; o = align_up(o + sizeof(float) * (size_t)P.ld2_total, 256);
     P.off_keys = o;
-    o = align_up(o + (spatial ? sizeof(u64) * (size_t)P.total_items * TILE * 5 : argmin_ws_bytes(P.ld2_total, k, npairs)), 256);
+    o = align_up(o + (spatial ? top5_ws_bytes(P.total_items, P.total_ytiles) : argmin_ws_bytes(P.ld2_total, k, npairs)), 256);
     if (spatial) {
         P.off_cand = o;
         if (own_cand) o = align_up(o + sizeof(int64_t) * 2 * (size_t)P.cand_total, 256);

@@ -54,7 +54,7 @@ size_t f2p_nn_workspace_bytes(int n1, int n2, int k, int top5) {
     const int nrt = (n1 + TILE - 1) / TILE, nct = (n2 + TILE - 1) / TILE;
     const int ns = pick_nsplit(nrt, nct);
     size_t b = 256;
-    if (top5) b += sizeof(unsigned long long) * (size_t)nct * ns * TILE * 5;
+    if (top5) b += top5_ws_bytes((int64_t)nct * ns, nct);
     else b += argmin_ws_bytes((int64_t)nct * TILE, k, 1);
     return (b + 255) & ~(size_t)255;
 }

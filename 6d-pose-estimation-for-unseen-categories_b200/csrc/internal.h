@@ -29,6 +29,7 @@ struct ArgminWs {
     uint32_t* best2; int* flagged; int* nflag;
 };
 size_t nn_smem_bytes(int k, int mode);
+size_t top5_ws_bytes(int64_t total_items, int64_t total_ytiles);
 size_t argmin_ws_bytes(int64_t ld2_total, int k, int npairs);
 void argmin_ws_carve(ArgminWs& w, unsigned char* base, int64_t ld2_total, int k, int npairs);
 int launch_argmin(const float* xT, int64_t ld1_total, const float* nx, const float* yT, int64_t ld2_total,

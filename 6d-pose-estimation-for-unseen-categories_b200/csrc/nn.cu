@@ -30,6 +30,8 @@ struct NNParams {
     u64* part5;          // MODE 1: [total_items][TILE][5] keys
     uint32_t* best2;     // MODE 2: [ld2_total] bits of the second-smallest clamped d2 per column, pre-set to +inf bits
     const int* ncols;    // MODE 0 re-check pass: per-pair number of (compacted) columns to process, or null = n2
+    int* tileflag;       // [total column tiles]: gated kernel sets 1 when a candidate list overflowed; MODE 0/1 launched
+                         // as the exact fallback process only flagged column tiles (null = process everything)
 };
 
 constexpr uint32_t IDX_NONE = 0x7fffffffu;
@@ -91,6 +93,7 @@ nn_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUte
     const int xcol = pdp->x_col0, ycol = pdp->y_col0 + ct * TILE;
     const int total_stages = ntiles * nkc;
     if (ct * TILE >= pd_n2) return;   // re-check pass: fewer compacted columns than the grid was sized for (uniform exit)
+    if (MODE != 2 && prm.tileflag && prm.tileflag[pdp->ytile0 + ct] == 0) return;   // exact fallback: flagged tiles only
 
     if (tid == 0) {
         tma_prefetch_desc(&mapX);
@@ -317,6 +320,305 @@ nn_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUte
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// Gated kernel (the fast path of both solvers): same operand staging and FFMA2 main loop as nn_kernel, but the
+// epilogue does NOT track minima per element.  Every column keeps a threshold tau_j = raw clamped d2 of its current
+// K-th best candidate (K = 1: arg-min, K = 5: top-5); an element costs one packed add pair and one compare, and only
+// the rare elements below tau are appended to a small per-column candidate list in shared memory.  After every row
+// tile the lists are cut back to the exact K best by (sqrt_rn(d2), row) and tau is lowered.
+//
+// Exactness: rows arrive in ascending tile order, so a later row can only enter a column's top K when its distance is
+// STRICTLY smaller than the current K-th distance (equal distances lose to the lower index already held), hence
+// sqrt(d2') < sqrt(d2_K)  =>  d2' < d2_K = tau: the strict raw-value gate never drops a winner, and the cut itself
+// orders by the exact (sqrt_rn, row) key.  Square roots are taken for list entries only.
+// A list that overflows (more than CAP - K appends to one column within one tile: rows arriving sorted by decreasing
+// distance) flags its column tile; the exact kernel (nn_kernel<0/1>) then redoes flagged tiles, so the result is
+// exact for every input and fast for every realistic one.
+// ---------------------------------------------------------------------------------------------------------------
+template <int K> struct GatedCfg { static constexpr int CAP = (K == 1) ? 1 : 32; };   // K == 1 keeps no lists
+
+template <int K, int CAP>
+__device__ __forceinline__ void gated_append(int col, float v, uint32_t row, float* s_val, uint32_t* s_row, int* s_cnt,
+                                             int* s_ovf) {
+    const int slot = atomicAdd(&s_cnt[col], 1);
+    if (slot < CAP) { s_val[slot * TILE + col] = fmaxf(v, 0.f); s_row[slot * TILE + col] = row; }
+    else *s_ovf = 1;
+}
+
+// K = 1 only: a passing candidate is merged straight into the column's exact (sqrt_rn(d2), row) key with a 64-bit
+// shared-memory atomicMin (no list, no cut, nothing to overflow) and lowers the column's threshold immediately.  Rows of one tile are processed in no
+// particular index order, so the new threshold must still admit every value whose sqrt_rn equals the candidate's
+// (a lower-index row with the same distance wins the tie): tau' = up((s + 1 ulp)^2) with s = sqrt_rn(c) is above the
+// whole rounding class of s, and any x >= tau' has sqrt_rn(x) > s.
+__device__ __forceinline__ void gated_best1(int col, float v, uint32_t row, float* s_tau, u64* s_best) {
+    const float sr = __fsqrt_rn(fmaxf(v, 0.f));
+    atomicMin(s_best + col, make_key(sr, row));
+    const float su = __uint_as_float(__float_as_uint(sr) + 1u);
+    atomicMin(reinterpret_cast<unsigned*>(s_tau) + col, __float_as_uint(__fmul_ru(su, su)));
+}
+
+// one thread per column: cut the list back to the K best by (sqrt_rn(d2), row), lower tau
+template <int K, int CAP>
+__device__ __forceinline__ void gated_compact(int col, float* s_val, uint32_t* s_row, int* s_cnt, float* s_tau, int& kept) {
+    int n = s_cnt[col];
+    if (n == kept) return;                 // nothing appended since the last cut
+    if (n > CAP) n = CAP;                  // overflow: already flagged by the appender
+    u64 key[K]; float raw[K];
+#pragma unroll
+    for (int r = 0; r < K; ++r) { key[r] = ~0ull; raw[r] = __int_as_float(0x7f800000); }
+    for (int e = 0; e < n; ++e) {
+        float rv = s_val[e * TILE + col];
+        u64 kk = make_key(__fsqrt_rn(rv), s_row[e * TILE + col]);
+#pragma unroll
+        for (int r = 0; r < K; ++r) {
+            const bool p = kk < key[r];
+            const u64 tk = key[r]; const float tr = raw[r];
+            key[r] = p ? kk : tk; raw[r] = p ? rv : tr;
+            kk = p ? tk : kk; rv = p ? tr : rv;
+        }
+    }
+    const int m = n < K ? n : K;
+#pragma unroll
+    for (int r = 0; r < K; ++r)
+        if (r < m) { s_val[r * TILE + col] = raw[r]; s_row[r * TILE + col] = (uint32_t)(key[r] & 0xffffffffull); }
+    s_cnt[col] = m;
+    kept = m;
+    if (m == K) s_tau[col] = raw[K - 1];
+}
+
+template <int K, int KC, int NSTAGE>
+__global__ void __launch_bounds__(NN_THREADS, 2)
+nn_gated_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapY, const NNParams prm) {
+    constexpr int CAP = GatedCfg<K>::CAP;
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    const int k = prm.k;
+    const int nkc = (k + KC - 1) / KC;
+    float* sB = reinterpret_cast<float*>(smem_raw);                 // [nkc*KC][TILE]
+    float* sA = sB + (size_t)nkc * KC * TILE;                        // NSTAGE x [KC][TILE]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sA + (size_t)NSTAGE * KC * TILE);
+    uint64_t* fullB = bars;
+    uint64_t* full = bars + 1;
+    uint64_t* empty = bars + 1 + NSTAGE;
+    float* s_tau = reinterpret_cast<float*>(bars + 16);              // [TILE]
+    int* s_cnt = reinterpret_cast<int*>(s_tau + TILE);               // [TILE]
+    float* s_val = reinterpret_cast<float*>(s_cnt + TILE);           // [CAP][TILE] raw clamped d2
+    uint32_t* s_row = reinterpret_cast<uint32_t*>(s_val + CAP * TILE);   // [CAP][TILE]
+    int* s_ovf = reinterpret_cast<int*>(s_row + CAP * TILE);
+    u64* s_best = reinterpret_cast<u64*>(s_cnt);                     // K == 1: [TILE] exact keys (lists unused)
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tx = ((warp & 1) << 3) | (lane & 7);
+    const int ty = ((warp >> 1) << 2) | ((lane >> 4) << 1) | ((lane >> 3) & 1);
+
+    const int item = blockIdx.x;
+    const int pi = find_pair(item, prm.pairs, prm.npairs, prm.uniform_items, &PairDev::item0);
+    const PairDev* pdp = prm.pairs + pi;
+    const int pd_nsplit = pdp->nsplit, pd_nrt = pdp->nrt, pd_n2 = pdp->n2;
+    const int local = item - pdp->item0;
+    const int ct = local / pd_nsplit, sp = local - ct * pd_nsplit;
+    const int t_begin = (int)(((long long)sp * pd_nrt) / pd_nsplit);
+    const int t_end = (int)(((long long)(sp + 1) * pd_nrt) / pd_nsplit);
+    const int ntiles = t_end - t_begin;
+    const int xcol = pdp->x_col0, ycol = pdp->y_col0 + ct * TILE;
+    const int total_stages = ntiles * nkc;
+    const float INF = __int_as_float(0x7f800000);
+
+    if (tid == 0) {
+        tma_prefetch_desc(&mapX);
+        tma_prefetch_desc(&mapY);
+        mbar_init(fullB, 1);
+        for (int s = 0; s < NSTAGE; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], NN_THREADS / 32); }
+        fence_barrier_init();
+        *s_ovf = 0;
+    }
+    if (tid < TILE) {
+        s_tau[tid] = INF;
+        if (K == 1) s_best[tid] = ~0ull; else s_cnt[tid] = 0;
+    }
+    __syncthreads();
+
+    auto issue = [&](int s) {
+        const int slot = s % NSTAGE, t = s / nkc, kc = s - t * nkc;
+        mbar_arrive_expect_tx(&full[slot], KC * TILE * sizeof(float));
+        tma_load_2d(sA + (size_t)slot * KC * TILE, &mapX, xcol + (t_begin + t) * TILE, kc * KC, &full[slot]);
+    };
+    if (tid == PRODUCER_TID) {
+        mbar_arrive_expect_tx(fullB, (uint32_t)(nkc * KC * TILE * sizeof(float)));
+        for (int kc = 0; kc < nkc; ++kc) tma_load_2d(sB + (size_t)kc * KC * TILE, &mapY, ycol, kc * KC, fullB);
+        for (int s = 0; s < NSTAGE && s < total_stages; ++s) issue(s);
+    }
+
+    u64 ny2[4];
+    {
+        const float4 n0 = __ldg(reinterpret_cast<const float4*>(prm.ny + ycol + tx * 4));
+        const float4 n1 = __ldg(reinterpret_cast<const float4*>(prm.ny + ycol + 64 + tx * 4));
+        ny2[0] = pack2(n0.x, n0.y); ny2[1] = pack2(n0.z, n0.w);
+        ny2[2] = pack2(n1.x, n1.y); ny2[3] = pack2(n1.z, n1.w);
+    }
+    float tau[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) tau[j] = INF;
+    int kept = 0;                          // threads < TILE: entries their column held after its last cut
+
+    mbar_wait(fullB, 0);
+
+    int s = 0;
+    for (int t = 0; t < ntiles; ++t) {
+        const int rowbase = (t_begin + t) * TILE;
+        const float4 nxa = __ldg(reinterpret_cast<const float4*>(prm.nx + xcol + rowbase + ty * 4));
+        const float4 nxb = __ldg(reinterpret_cast<const float4*>(prm.nx + xcol + rowbase + 64 + ty * 4));
+        u64 acc[8][4];
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j] = 0ull;
+
+        for (int kc = 0; kc < nkc; ++kc, ++s) {
+            const int slot = s % NSTAGE;
+            const uint32_t ph = (uint32_t)((s / NSTAGE) & 1);
+            if (tid == PRODUCER_TID && s >= 1) {
+                const int sn = s - 1 + NSTAGE;
+                if (sn < total_stages) {
+                    mbar_wait(&empty[(s - 1) % NSTAGE], (uint32_t)(((s - 1) / NSTAGE) & 1));
+                    issue(sn);
+                }
+            }
+            mbar_wait(&full[slot], ph);
+            const float* A = sA + (size_t)slot * KC * TILE + ty * 4;
+            const float* B = sB + (size_t)kc * KC * TILE + tx * 4;
+            const int klen = min(KC, k - kc * KC);
+            auto step = [&](int kk) {
+                const float4 a0 = *reinterpret_cast<const float4*>(A + kk * TILE);
+                const float4 a1 = *reinterpret_cast<const float4*>(A + kk * TILE + 64);
+                const ulonglong2 b0 = *reinterpret_cast<const ulonglong2*>(B + kk * TILE);
+                const ulonglong2 b1 = *reinterpret_cast<const ulonglong2*>(B + kk * TILE + 64);
+                const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+                const u64 bp[4] = {b0.x, b0.y, b1.x, b1.y};
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) fma2v(acc[i][j], pack2(av[i], av[i]), bp[j]);
+            };
+            if (klen == KC) {
+#pragma unroll
+                for (int kk = 0; kk < KC; ++kk) step(kk);
+            } else {
+                for (int kk = 0; kk < klen; ++kk) step(kk);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[slot]);
+        }
+
+        const float nxv[8] = {nxa.x, nxa.y, nxa.z, nxa.w, nxb.x, nxb.y, nxb.z, nxb.w};
+        // row i of this thread: values (acc + nx) + ny for its 8 columns, gate against tau, append the rare passes
+        auto gate_row = [&](int i) {
+            const uint32_t row = (uint32_t)(rowbase + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4)));
+            const u64 nn = pack2(nxv[i], nxv[i]);
+            float v[8];
+#pragma unroll
+            for (int jp = 0; jp < 4; ++jp) unpack2(add2(add2(acc[i][jp], nn), ny2[jp]), v[2 * jp], v[2 * jp + 1]);
+            if (K == 1) {
+                // arg-min: tau is re-read from shared memory for every row, because appenders lower it at once
+                // (see gated_append_lower) — a stale threshold lets (n_new / n_seen)^m columns collect m appends
+                const float4 t0 = *reinterpret_cast<const float4*>(s_tau + tx * 4);
+                const float4 t1 = *reinterpret_cast<const float4*>(s_tau + 64 + tx * 4);
+                tau[0] = t0.x; tau[1] = t0.y; tau[2] = t0.z; tau[3] = t0.w;
+                tau[4] = t1.x; tau[5] = t1.y; tau[6] = t1.z; tau[7] = t1.w;
+            }
+            bool any = false;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) any |= (v[j] < tau[j]);
+            if (any) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    if (v[j] < tau[j]) {
+                        const int col = j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4);
+                        if (K == 1) gated_best1(col, v[j], row, s_tau, s_best);
+                        else gated_append<K, CAP>(col, v[j], row, s_val, s_row, s_cnt, s_ovf);
+                    }
+            }
+        };
+        auto cut_and_reload = [&]() {
+            __syncthreads();
+            if (tid < TILE) gated_compact<K, CAP>(tid, s_val, s_row, s_cnt, s_tau, kept);
+            __syncthreads();
+            const float4 t0 = *reinterpret_cast<const float4*>(s_tau + tx * 4);
+            const float4 t1 = *reinterpret_cast<const float4*>(s_tau + 64 + tx * 4);
+            tau[0] = t0.x; tau[1] = t0.y; tau[2] = t0.z; tau[3] = t0.w;
+            tau[4] = t1.x; tau[5] = t1.y; tau[6] = t1.z; tau[7] = t1.w;
+        };
+
+        if (t == 0) {
+            // bootstrap (tau = +inf): bounded appends per cut so the first tile cannot overflow
+            if (K == 1) {
+                // exact local arg-min over this thread's 8 rows, merged across the 4 lanes sharing a column:
+                // at most 4 entries per column
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    float bd = INF, braw = INF; uint32_t bi = IDX_NONE;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        float v0, v1;
+                        unpack2(add2(add2(acc[i][j >> 1], pack2(nxv[i], nxv[i])), ny2[j >> 1]), v0, v1);
+                        const float c = fmaxf((j & 1) ? v1 : v0, 0.f);
+                        const float d = __fsqrt_rn(c);
+                        const bool p = d < bd;
+                        bd = p ? d : bd; braw = p ? c : braw;
+                        bi = p ? (uint32_t)(rowbase + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4))) : bi;
+                    }
+                    u64 key = make_key(bd, bi);
+#pragma unroll
+                    for (int m = 8; m <= 16; m <<= 1) {
+                        const u64 ok = shfl_xor_u64(key, m);
+                        const float oraw = __shfl_xor_sync(0xffffffffu, braw, m);
+                        const bool p = ok < key;
+                        key = p ? ok : key; braw = p ? oraw : braw;
+                    }
+                    const uint32_t wi = (uint32_t)(key & 0xffffffffull);
+                    if ((lane & 24) == 0 && wi != IDX_NONE)
+                        gated_best1(j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4), braw, wi, s_tau, s_best);
+                }
+            } else {
+                // one row of every thread per cut: at most 16 appends per column on top of the K kept
+                for (int step_i = 0; step_i < 8; ++step_i) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        if (i == step_i) gate_row(i);
+                    cut_and_reload();
+                }
+            }
+        } else if (K != 1 && t == 1) {
+            // the threshold is still loose (K-th best of 128 rows): two cuts keep the (n_new / n_seen)^m tail of
+            // the append count away from CAP
+#pragma unroll
+            for (int i = 0; i < 4; ++i) gate_row(i);
+            cut_and_reload();
+#pragma unroll
+            for (int i = 4; i < 8; ++i) gate_row(i);
+            cut_and_reload();
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) gate_row(i);
+            if (K != 1) cut_and_reload();        // K == 1 runs without any CTA-wide synchronisation
+        }
+    }
+
+    // ---- results: the lists hold the exact K best of this CTA's rows, sorted by (distance, row) ------------------
+    if (K == 1) {
+        __syncthreads();
+        if (tid < TILE && ct * TILE + tid < pd_n2) atomicMin(prm.best + ycol + tid, s_best[tid]);
+    } else {
+        if (tid < TILE) {
+#pragma unroll
+            for (int r = 0; r < K; ++r)
+                prm.part5[((size_t)item * TILE + tid) * 5 + r] =
+                    r < kept ? make_key(__fsqrt_rn(s_val[r * TILE + tid]), s_row[r * TILE + tid]) : ~0ull;
+        }
+        if (tid == 0 && *s_ovf) prm.tileflag[pdp->ytile0 + ct] = 1;
+    }
+}
+
 // ---- finalize: keys -> int64 index maps ---------------------------------------------------------------
 __device__ __forceinline__ int64_t row1_value(int j, unsigned flags) {
     // linspace(0,V2-1,V2).type(int16) promoted to int64 (naive.py:21): wraps modulo 2^16 on the reference's CPU path
@@ -333,7 +635,7 @@ finalize_argmin_kernel(const u64* __restrict__ best, const PairDev* __restrict__
     const int n2 = pd->n2;
     if (j >= n2) return;
     uint32_t idx = (uint32_t)(best[pd->y_col0 + j] & 0xffffffffull);
-    if (idx == IDX_NONE) idx = 0;  // all distances were +inf/NaN: out of contract, mirror argmin's first index
+    if (idx >= IDX_NONE) idx = 0;  // all distances were +inf/NaN: out of contract, mirror argmin's first index
     int64_t* o = out + pd->out_off;
     o[j] = (int64_t)idx;
     if (!(flags & F2P_ROW0_ONLY)) o[(int64_t)n2 + j] = row1_value(j, flags);
@@ -370,12 +672,14 @@ finalize_top5_kernel(const u64* __restrict__ part5, const PairDev* __restrict__ 
 
 // ---- two-phase arg-min support kernels ----------------------------------------------------------------
 // Initialises the per-column merge state of an arg-min pass (and the per-pair re-check counters).
-__global__ void argmin_init_kernel(u64* best, uint32_t* best2, u64* best_exact, size_t n, int* nflag, int npairs) {
+__global__ void argmin_init_kernel(u64* best, uint32_t* best2, u64* best_exact, size_t n, int* nflag, int npairs,
+                                   int* tileflag) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) {
         best[i] = ~0ull;
         if (best2) best2[i] = 0x7f800000u;
         if (best_exact) best_exact[i] = ~0ull;
+        if (tileflag && i < n / TILE) tileflag[i] = 0;
     }
     if (nflag && i < (size_t)npairs) nflag[i] = 0;
 }
@@ -448,6 +752,9 @@ static size_t nn_smem_bytes_v(int k, int mode, int kc, int nst) {
     return b;
 }
 size_t nn_smem_bytes(int k, int mode) { return nn_smem_bytes_v(k, mode, KC, NSTAGE); }
+size_t top5_ws_bytes(int64_t total_items, int64_t total_ytiles) {
+    return sizeof(u64) * (size_t)total_items * TILE * 5 + sizeof(int) * (size_t)total_ytiles;
+}
 
 template <int MODE>
 static int launch_mode(const float* xT, int64_t ld1_total, const float* yT, int64_t ld2_total, int k, const NNParams& prm,
@@ -460,6 +767,28 @@ static int launch_mode(const float* xT, int64_t ld1_total, const float* yT, int6
     const size_t smem = nn_smem_bytes_v(k, MODE, KC, NSTAGE);
     F2P_CUDA(cudaFuncSetAttribute(nn_kernel<MODE, KC, NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     nn_kernel<MODE, KC, NSTAGE><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);
+    F2P_CUDA(cudaGetLastError());
+    return 0;
+}
+
+template <int K>
+static size_t gated_smem_bytes(int k) {
+    const int nkc = (k + KC - 1) / KC;
+    return ((size_t)nkc * KC * TILE + (size_t)NSTAGE * KC * TILE) * sizeof(float) + 16 * sizeof(uint64_t) +
+           2 * TILE * sizeof(int) + (size_t)GatedCfg<K>::CAP * TILE * 8 + 16;
+}
+
+template <int K>
+static int launch_gated(const float* xT, int64_t ld1_total, const float* yT, int64_t ld2_total, int k, const NNParams& prm,
+                        int total_items, cudaStream_t stream) {
+    CUtensorMap mapX, mapY;
+    int rc = make_tensor_map_2d(&mapX, xT, (uint64_t)ld1_total, (uint64_t)k, (uint64_t)ld1_total, TILE, KC);
+    if (rc) return rc;
+    rc = make_tensor_map_2d(&mapY, yT, (uint64_t)ld2_total, (uint64_t)k, (uint64_t)ld2_total, TILE, KC);
+    if (rc) return rc;
+    const size_t smem = gated_smem_bytes<K>(k);
+    F2P_CUDA(cudaFuncSetAttribute(nn_gated_kernel<K, KC, NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    nn_gated_kernel<K, KC, NSTAGE><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);
     F2P_CUDA(cudaGetLastError());
     return 0;
 }
@@ -489,12 +818,14 @@ void argmin_ws_carve(ArgminWs& w, unsigned char* base, int64_t ld2_total, int k,
     w.nflag = reinterpret_cast<int*>(p);
 }
 
-// Two-phase threshold: below this much arithmetic the extra launches of the re-check path cost more than the
-// square roots they save, so the exact kernel runs directly.
-static bool use_two_phase(double flops) {
-    const char* e = getenv("F2P_ARGMIN_TWO_PHASE");   // test/override switch: "0" exact pass only, "1" always two-phase
-    if (e && (e[0] == '0' || e[0] == '1')) return e[0] == '1';
-    return flops >= 5e9;
+// Path switch (tests): F2P_NN_PATH = "exact" (nn_kernel<0/1> alone), "two_phase" (arg-min: raw pass + re-check of
+// sqrt-ambiguous columns), "gated" (default: threshold-gated kernel + exact fallback for overflowed column tiles).
+enum NNPath { PATH_GATED = 0, PATH_EXACT = 1, PATH_TWO_PHASE = 2 };
+static NNPath nn_path() {
+    const char* e = getenv("F2P_NN_PATH");
+    if (e && e[0] == 'e') return PATH_EXACT;
+    if (e && e[0] == 't') return PATH_TWO_PHASE;
+    return PATH_GATED;
 }
 
 int launch_argmin(const float* xT, int64_t ld1_total, const float* nx, const float* yT, int64_t ld2_total,
@@ -505,17 +836,26 @@ int launch_argmin(const float* xT, int64_t ld1_total, const float* nx, const flo
     NNParams prm;
     prm.pairs = pairs_dev; prm.npairs = npairs; prm.uniform_items = uniform_items; prm.k = k;
     prm.nx = nx; prm.ny = ny; prm.best = w.best; prm.part5 = nullptr; prm.best2 = nullptr; prm.ncols = nullptr;
-    const bool two = use_two_phase(flops);
+    prm.tileflag = nullptr;
+    const NNPath path = nn_path();
+    (void)flops;
     const unsigned iblocks = (unsigned)((ld2_total + 255) / 256);
     int rc;
-    if (!two) {
-        argmin_init_kernel<<<iblocks, 256, 0, stream>>>(w.best, nullptr, nullptr, (size_t)ld2_total, nullptr, 0);
+    if (path == PATH_GATED) {
+        argmin_init_kernel<<<iblocks, 256, 0, stream>>>(w.best, nullptr, nullptr, (size_t)ld2_total, nullptr, 0, nullptr);
+        if ((rc = launch_gated<1>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream))) return rc;   // exact, no fallback
+        finalize_argmin_kernel<<<total_ytiles, TILE, 0, stream>>>(w.best, pairs_dev, npairs, uniform_ytiles, flags, out);
+        F2P_CUDA(cudaGetLastError());
+        return 0;
+    }
+    if (path == PATH_EXACT) {
+        argmin_init_kernel<<<iblocks, 256, 0, stream>>>(w.best, nullptr, nullptr, (size_t)ld2_total, nullptr, 0, nullptr);
         if ((rc = launch_mode<0>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream))) return rc;
         finalize_argmin_kernel<<<total_ytiles, TILE, 0, stream>>>(w.best, pairs_dev, npairs, uniform_ytiles, flags, out);
         F2P_CUDA(cudaGetLastError());
         return 0;
     }
-    argmin_init_kernel<<<iblocks, 256, 0, stream>>>(w.best, w.best2, w.best_exact, (size_t)ld2_total, w.nflag, npairs);
+    argmin_init_kernel<<<iblocks, 256, 0, stream>>>(w.best, w.best2, w.best_exact, (size_t)ld2_total, w.nflag, npairs, nullptr);
     prm.best2 = w.best2;
     if ((rc = launch_mode<2>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream))) return rc;
     finalize_raw_kernel<<<total_ytiles, TILE, 0, stream>>>(w.best, w.best2, pairs_dev, npairs, uniform_ytiles, flags, out,
@@ -538,7 +878,15 @@ int launch_top5(const float* xT, int64_t ld1_total, const float* nx, const float
     NNParams prm;
     prm.pairs = pairs_dev; prm.npairs = npairs; prm.uniform_items = uniform_items; prm.k = k;
     prm.nx = nx; prm.ny = ny; prm.best = nullptr; prm.part5 = part5; prm.best2 = nullptr; prm.ncols = nullptr;
-    int rc = launch_mode<1>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
+    prm.tileflag = nullptr;
+    int rc;
+    if (nn_path() == PATH_GATED) {
+        // tile flags follow the partial lists in the workspace (top5_ws_bytes)
+        prm.tileflag = reinterpret_cast<int*>(part5 + (size_t)total_items * TILE * 5);
+        F2P_CUDA(cudaMemsetAsync(prm.tileflag, 0, sizeof(int) * (size_t)total_ytiles, stream));
+        if ((rc = launch_gated<5>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream))) return rc;
+    }
+    rc = launch_mode<1>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);   // gated path: flagged tiles only
     if (rc) return rc;
     finalize_top5_kernel<<<total_ytiles, TILE, 0, stream>>>(part5, pairs_dev, npairs, uniform_ytiles, flags, cand, cand_is_out_layout);
     F2P_CUDA(cudaGetLastError());

@@ -32,10 +32,18 @@ def oracle():
     return O
 
 
-@pytest.fixture(params=["exact", "two_phase"])
+@pytest.fixture(params=["gated", "exact", "two_phase"])
 def argmin_path(request, monkeypatch):
-    """Runs a test through both arg-min paths: the exact kernel alone and raw pass + re-check of ambiguous columns."""
-    monkeypatch.setenv("F2P_ARGMIN_TWO_PHASE", "1" if request.param == "two_phase" else "0")
+    """Runs a test through every arg-min path: the threshold-gated kernel (default), the exact kernel alone, and the
+    raw pass + re-check of sqrt-ambiguous columns."""
+    monkeypatch.setenv("F2P_NN_PATH", request.param)
+    return request.param
+
+
+@pytest.fixture(params=["gated", "exact"])
+def top5_path(request, monkeypatch):
+    """Runs a spatial test through the threshold-gated top-5 kernel (default) and the exact register-list kernel."""
+    monkeypatch.setenv("F2P_NN_PATH", request.param)
     return request.param
 
 
@@ -112,7 +120,7 @@ def test_naive_batched_ragged(solvers, oracle, argmin_path):
 
 # ---------------------------------------------------------------------------------------------- spatial
 @pytest.mark.parametrize("name", SPATIAL)
-def test_spatial_matches_reference_golden(solvers, golden, name, capsys):
+def test_spatial_matches_reference_golden(solvers, golden, name, capsys, top5_path):
     from fmap2pointmap_solvers.batched import spatial_batched
     c, inp = load_case(golden, name)
     d = _cuda(inp)
@@ -127,7 +135,7 @@ def test_spatial_matches_reference_golden(solvers, golden, name, capsys):
 
 
 @pytest.mark.parametrize("shape", [(5, 1, 4), (40, 7, 8), (300, 33, 30), (600, 257, 30), (900, 410, 50), (3000, 820, 64)])
-def test_spatial_edge_shapes_vs_oracle(solvers, oracle, shape):
+def test_spatial_edge_shapes_vs_oracle(solvers, oracle, shape, top5_path):
     from fmap2pointmap_solvers.synth import make_pair
     n1, n2, k = shape
     P = make_pair(n1, n2, k, seed=700 + n1 + n2)
@@ -138,7 +146,7 @@ def test_spatial_edge_shapes_vs_oracle(solvers, oracle, shape):
         np.testing.assert_array_equal(got, oracle.spatial(P.C12, P.evecs_x, P.evecs_y, P.CAD, P.PC, diam))
 
 
-def test_spatial_batched_ragged(solvers, oracle):
+def test_spatial_batched_ragged(solvers, oracle, top5_path):
     from fmap2pointmap_solvers.batched import spatial_batched
     from fmap2pointmap_solvers.synth import make_pair
     shapes = [(300, 200), (1000, 64), (129, 300), (50, 5), (2048, 700)]
@@ -223,3 +231,81 @@ def test_kernel3_vote_scores_bits_and_mask(solvers, oracle, M):
     # survivors are a subsequence of the original columns
     cols = {(int(a), int(b)) for a, b in want.T}
     assert int(mask.sum()) == m
+
+
+@pytest.mark.parametrize("scale", [1e-16, 3e-19, 1e-22])
+def test_kernel3_vote_tiny_nonzero_and_zero_distances(solvers, oracle, scale):
+    """Squared distances that are exactly zero (shared CAD vertex / scene point) stay on the packed fast path; nonzero
+    ones below 2^-101 (coordinates ~1e-16 apart and smaller, down to subnormal squares) must take the full-range
+    sqrt_rn redo.  Scores are compared bit for bit with the oracle."""
+    from fmap2pointmap_solvers import _lib
+    L = _lib.load()
+    M = 700
+    g = torch.Generator().manual_seed(77)
+    ncad, npc = 90, 150                       # few distinct vertices: many exact-zero A distances
+    CAD = torch.rand(ncad, 3, generator=g) * 10
+    CAD[:40] = torch.rand(40, 3, generator=g) * scale          # a cluster of nearly coincident vertices
+    CAD[40:50] = CAD[:10]                                      # and exact duplicates of some of them
+    PC = torch.rand(npc, 3, generator=g) * 10
+    PC[:60] = torch.rand(60, 3, generator=g) * scale * 3
+    p0 = torch.randint(0, ncad, (M,), generator=g)
+    p1 = torch.sort(torch.randint(0, npc, (M,), generator=g)).values
+    p = torch.stack([p0, p1], 0).contiguous()
+    thr = (ctypes.c_float * 4)(1e30, 1e30, 1e30, 1e30)
+    out = torch.zeros(2, M, dtype=torch.int64, device="cuda")
+    meta = torch.zeros(2, dtype=torch.int32, device="cuda")
+    scores = torch.full((3, M), float("nan"), device="cuda")
+    ws = _ws(L.f2p_filter_workspace_bytes(M))
+    cd, pd, pp = CAD.cuda(), PC.cuda(), p.cuda()
+    rc = L.f2p_spatial_filter(cd.data_ptr(), ncad, pd.data_ptr(), npc, pp.data_ptr(), M, thr, out.data_ptr(),
+                              meta.data_ptr(), meta.data_ptr() + 4, None, scores.data_ptr(), ws.data_ptr(),
+                              ws.numel(), None)
+    _lib.check(rc, "f2p_spatial_filter")
+    torch.cuda.synchronize()
+    s0 = oracle.vote_scores(CAD[p0], PC[p1])
+    for r in range(3):                        # nothing is pruned, so every round repeats the same scores
+        np.testing.assert_array_equal(scores[r].cpu().numpy().view(np.int32), s0.view(np.int32))
+    assert int(meta[0]) == M
+
+
+def _adversarial_pair(n1, n2, k, seed):
+    """Rows of feat_x sorted by DECREASING distance to every scene point (each new row beats all earlier ones), with
+    runs of exactly duplicated rows: the gated kernel's candidate lists overflow and the exact fallback must take over."""
+    g = torch.Generator().manual_seed(seed)
+    u = torch.randn(k, generator=g)
+    u /= u.norm()
+    scale = torch.linspace(3.0, 1.0, n1).unsqueeze(1)
+    ex = scale * u + 1e-3 * torch.randn(n1, k, generator=g)
+    ex[n1 // 2: n1 // 2 + 40] = ex[n1 // 2]                      # exact ties: lowest index must win
+    ey = 0.05 * torch.randn(n2, k, generator=g)
+    C = torch.eye(k)
+    return C, ex.contiguous(), ey.contiguous()
+
+
+@pytest.mark.parametrize("shape", [(1500, 300, 16), (4000, 130, 50)])
+def test_naive_overflowing_lists_fall_back_exactly(solvers, oracle, shape):
+    C, ex, ey = _adversarial_pair(*shape, seed=5)
+    got = solvers.naive_fmap2pointmap(C.cuda(), ex.cuda(), ey.cuda()).cpu().numpy()
+    np.testing.assert_array_equal(got, oracle.naive(C, ex, ey, int16_compat=False))
+
+
+@pytest.mark.parametrize("shape", [(1500, 300, 16), (4000, 130, 50)])
+def test_top5_overflowing_lists_fall_back_exactly(solvers, oracle, shape):
+    from fmap2pointmap_solvers import _lib
+    L = _lib.load()
+    n1, n2, k = shape
+    C, ex, ey = _adversarial_pair(n1, n2, k, seed=6)
+    ld1, ld2 = (n1 + 127) // 128 * 128, (n2 + 127) // 128 * 128
+    xT = torch.empty(k, ld1, device="cuda"); nx = torch.empty(ld1, device="cuda")
+    yT = torch.empty(k, ld2, device="cuda"); ny = torch.empty(ld2, device="cuda")
+    ws = _ws(L.f2p_project_workspace_bytes())
+    exd, eyd, Cd = ex.cuda(), ey.cuda(), C.cuda()
+    _lib.check(L.f2p_project(exd.data_ptr(), n1, k, k, Cd.data_ptr(), xT.data_ptr(), nx.data_ptr(), ld1, ws.data_ptr(), ws.numel(), None), "f2p_project")
+    _lib.check(L.f2p_project(eyd.data_ptr(), n2, k, k, None, yT.data_ptr(), ny.data_ptr(), ld2, ws.data_ptr(), ws.numel(), None), "f2p_project")
+    wsn = _ws(L.f2p_nn_workspace_bytes(n1, n2, k, 1))
+    out = torch.empty(5 * n2, dtype=torch.int64, device="cuda")
+    _lib.check(L.f2p_nn_top5(xT.data_ptr(), nx.data_ptr(), n1, ld1, yT.data_ptr(), ny.data_ptr(), n2, ld2, k, out.data_ptr(),
+                             wsn.data_ptr(), wsn.numel(), None), "f2p_nn_top5")
+    torch.cuda.synchronize()
+    want = oracle.nn_top5(oracle.project(ex, C), ey)
+    np.testing.assert_array_equal(out.cpu().numpy().reshape(n2, 5), want)
