@@ -105,11 +105,96 @@ class _Packed:
         self.out_total = out_off
 
 
+def thresholds_many(diam_cad, n):
+    """`thresholds` for n pairs at once ([n,4] float32), same type rules: FP32 tensor -> FP32 products, Python / NumPy
+    numbers -> FP64 products cast to FP32."""
+    import numpy as np
+    if isinstance(diam_cad, torch.Tensor):
+        d = diam_cad.detach().reshape(-1)
+        if d.numel() == 1:
+            d = d.expand(n)
+        if d.numel() != n:
+            raise ValueError("diam_cad must have one entry per pair")
+        return torch.stack([(c * d).to(torch.float32) for c in _FACTORS], 1).cpu().numpy()
+    if isinstance(diam_cad, (int, float)) or (hasattr(diam_cad, "dtype") and getattr(diam_cad, "ndim", 1) == 0):
+        diam_cad = [diam_cad] * n
+    if isinstance(diam_cad, np.ndarray) and diam_cad.dtype in (np.float64, np.float32) and diam_cad.shape == (n,):
+        return np.stack([(c * diam_cad).astype(np.float32) for c in _FACTORS], 1)
+    if len(diam_cad) != n:
+        raise ValueError("diam_cad must have one entry per pair")
+    if all(type(v) is float for v in diam_cad):
+        d = np.asarray(diam_cad, np.float64)
+        return np.stack([(c * d).astype(np.float32) for c in _FACTORS], 1)
+    return np.asarray([thresholds(v) for v in diam_cad], np.float32)
+
+
+def _is_stacked(x):
+    return isinstance(x, torch.Tensor) and x.dim() == 3
+
+
+class _PackedStacked:
+    """A uniform batch given as stacked tensors (C [P,k,k] or [k,k] shared, evecs_x [P,n1,k], evecs_y [P,n2,k],
+    CAD [P,ncad,3], PC [P,npc,3]): one device view per operand and a vectorised descriptor fill — no per-pair Python
+    work, and CPU inputs cost one H2D copy per operand."""
+
+    def __init__(self, C12, evecs_x, evecs_y, device, CAD=None, PC=None, diam_cad=None):
+        import numpy as np
+        ex = _lib.dev_f32(evecs_x, device).contiguous()
+        ey = _lib.dev_f32(evecs_y, device).contiguous()
+        n, n1, k = (int(v) for v in ex.shape)
+        n2 = int(ey.shape[1])
+        C = _lib.dev_f32(C12, device)
+        if C.dim() == 2:
+            C = C.unsqueeze(0)
+        if C.dim() == 4 and C.shape[1] == 1:
+            C = C.squeeze(1)
+        C = C.contiguous()
+        if C.dim() != 3 or C.shape[1] != k or C.shape[2] != k or C.shape[0] not in (1, n) or ey.shape[0] != n or ey.shape[2] != k:
+            raise RuntimeError(f"stacked batch: shapes C{tuple(C.shape)} evecs_x{tuple(ex.shape)} evecs_y{tuple(ey.shape)} are inconsistent")
+        self.n, self.k, self.n1, self.n2 = n, k, n1, n2
+        self.keep = [C, ex, ey]
+        self.C_base, self.ex_base, self.ey_base = C.data_ptr(), ex.data_ptr(), ey.data_ptr()
+        dt = np.dtype([("evecs_x_off", "<i8"), ("evecs_y_off", "<i8"), ("c_off", "<i8"), ("cad_off", "<i8"),
+                       ("pc_off", "<i8"), ("out_off", "<i8"), ("n1", "<i4"), ("n2", "<i4"), ("ldx", "<i4"),
+                       ("ldy", "<i4"), ("ncad", "<i4"), ("npc", "<i4"), ("thr", "<f4", (4,))])
+        assert dt.itemsize == ctypes.sizeof(_lib.F2PPairDesc)
+        d = np.zeros(max(n, 1), dt)
+        i = np.arange(max(n, 1), dtype=np.int64)
+        d["evecs_x_off"] = i * (n1 * k); d["evecs_y_off"] = i * (n2 * k)
+        d["c_off"] = 0 if C.shape[0] == 1 else i * (k * k)
+        d["n1"], d["n2"], d["ldx"], d["ldy"] = n1, n2, k, k
+        self.cad_base = self.pc_base = ex.data_ptr()
+        if CAD is not None:
+            cad = _lib.dev_f32(CAD, device).contiguous()
+            pc = _lib.dev_f32(PC, device).contiguous()
+            if cad.dim() == 2:
+                cad = cad.unsqueeze(0)
+            if cad.dim() != 3 or cad.shape[2] != 3 or pc.dim() != 3 or pc.shape[2] != 3 or pc.shape[0] != n or cad.shape[0] not in (1, n):
+                raise RuntimeError("stacked batch: CAD must be [P,ncad,3] (or one shared [ncad,3]) and PC [P,npc,3]")
+            self.keep += [cad, pc]
+            self.cad_base, self.pc_base = cad.data_ptr(), pc.data_ptr()
+            d["cad_off"] = 0 if cad.shape[0] == 1 else i * (int(cad.shape[1]) * 3)
+            d["pc_off"] = i * (int(pc.shape[1]) * 3)
+            d["ncad"], d["npc"] = int(cad.shape[1]), int(pc.shape[1])
+            d["thr"] = thresholds_many(diam_cad, n)
+            size = 10 * n2
+        else:
+            d["ncad"], d["npc"] = n1, n2
+            size = 2 * n2
+        d["out_off"] = i * size
+        self.desc_np = d
+        self.descs = d.ctypes.data_as(ctypes.POINTER(_lib.F2PPairDesc))
+        self.size = size
+        self.out_total = n * size
+
+
 def naive_batched(C12: Sequence[torch.Tensor], evecs_x: Sequence[torch.Tensor], evecs_y: Sequence[torch.Tensor],
                   int16_compat: bool = False) -> List[torch.Tensor]:
     """`naive_fmap2pointmap` (naive.py:5-21) for a list of pairs sharing K: one int64 [2,V2] tensor per pair, on the
     device of that pair's `evecs_x` (CPU inputs are copied to the current CUDA device and the result copied back)."""
     lib = _lib.load()
+    if _is_stacked(evecs_x):
+        return _naive_stacked(lib, C12, evecs_x, evecs_y, int16_compat)
     n = len(evecs_x)
     if n == 0:
         return []
@@ -144,6 +229,8 @@ def spatial_batched(C12: Sequence[torch.Tensor], evecs_x: Sequence[torch.Tensor]
     Returns one int64 [2,M'] tensor per pair (and, with return_info, per-pair dicts with the pre-filter candidates,
     the "skipped" flag and the status word).  The one host sync is the read of the survivor counts."""
     lib = _lib.load()
+    if _is_stacked(evecs_x):
+        return _spatial_stacked(lib, C12, evecs_x, evecs_y, CAD, PC, diam_cad, int16_compat, return_info, verbose)
     n = len(evecs_x)
     if n == 0:
         return ([], []) if return_info else []
@@ -174,7 +261,7 @@ def spatial_batched(C12: Sequence[torch.Tensor], evecs_x: Sequence[torch.Tensor]
             if status & 2:
                 raise IndexError(f"pair {i}: candidate index out of range of CAD/PC (CAD rows {d.ncad}, PC rows {d.npc})")
             M = 5 * d.n2
-            r = out[d.out_off:d.out_off + 2 * M].view(2, M)[:, :m].contiguous()
+            r = out[d.out_off:d.out_off + 2 * m].view(2, m)   # the library writes the survivors dense: a view, no copy
             if status & 1 and verbose:
                 print("skipped")  # spacial_filtering.py:70-71
             src = evecs_x[i]
@@ -183,4 +270,72 @@ def spatial_batched(C12: Sequence[torch.Tensor], evecs_x: Sequence[torch.Tensor]
                 c = cand[d.out_off:d.out_off + 2 * M].view(2, M)
                 infos.append({"candidates": c if src.is_cuda else c.to(src.device), "skipped": bool(status & 1),
                               "status": status})
+        return (res, infos) if return_info else res
+
+
+def _naive_stacked(lib, C12, evecs_x, evecs_y, int16_compat):
+    """Uniform batch as stacked tensors: returns ONE int64 [P,2,V2] tensor (index [i] = pair i's [2,V2] map)."""
+    device = _lib.cuda_device_for(evecs_x, evecs_y, C12)
+    with torch.cuda.device(device):
+        pk = _PackedStacked(C12, evecs_x, evecs_y, device)
+        if pk.n == 0 or pk.n2 == 0:
+            return torch.empty((pk.n, 2, pk.n2), dtype=torch.int64, device=evecs_x.device)
+        if pk.n1 < 1:
+            raise RuntimeError("evecs_x has no rows (argmin of an empty dimension)")
+        out = torch.empty(pk.out_total, dtype=torch.int64, device=device)
+        nbytes = lib.f2p_workspace_bytes(pk.descs, pk.n, pk.k, 0)
+        if nbytes == 0:
+            _lib.check(-1 if pk.k <= _lib.F2P_MAX_K else -3, "f2p_workspace_bytes")
+        ws = _lib.workspace(device, nbytes)
+        rc = lib.f2p_naive_batched(pk.ex_base, pk.ey_base, pk.C_base, pk.descs, pk.n, pk.k,
+                                   _lib.F2P_INT16_COMPAT if int16_compat else 0, out.data_ptr(), ws.data_ptr(),
+                                   ws.numel(), _lib.stream_ptr(device))
+        _lib.check(rc, "f2p_naive_batched")
+        res = out.view(pk.n, 2, pk.n2)
+        return res if evecs_x.is_cuda else res.to(evecs_x.device)
+
+
+def _spatial_stacked(lib, C12, evecs_x, evecs_y, CAD, PC, diam_cad, int16_compat, return_info, verbose):
+    """Uniform batch as stacked tensors.  Returns the list of per-pair int64 [2,M'] maps; each is a VIEW into one
+    flat result buffer (no per-pair copy kernels), on the input device."""
+    device = _lib.cuda_device_for(evecs_x, evecs_y, C12, CAD, PC)
+    with torch.cuda.device(device):
+        pk = _PackedStacked(C12, evecs_x, evecs_y, device, CAD, PC, diam_cad)
+        n = pk.n
+        if n == 0:
+            return ([], []) if return_info else []
+        out = torch.empty(max(pk.out_total, 1), dtype=torch.int64, device=device)
+        cand = torch.empty(max(pk.out_total, 1), dtype=torch.int64, device=device) if return_info else None
+        meta = torch.zeros(2 * n, dtype=torch.int32, device=device)
+        nbytes = lib.f2p_workspace_bytes(pk.descs, n, pk.k, 1)
+        if nbytes == 0:
+            rc = lib.f2p_spatial_batched(pk.ex_base, pk.ey_base, pk.C_base, pk.cad_base, pk.pc_base, pk.descs, n, pk.k, 0,
+                                         out.data_ptr(), meta.data_ptr(), meta.data_ptr() + 4 * n, None, out.data_ptr(),
+                                         0, _lib.stream_ptr(device))
+            _lib.check(rc if rc else -1, "f2p_spatial_batched")
+        ws = _lib.workspace(device, nbytes)
+        rc = lib.f2p_spatial_batched(pk.ex_base, pk.ey_base, pk.C_base, pk.cad_base, pk.pc_base, pk.descs, n, pk.k,
+                                     _lib.F2P_INT16_COMPAT if int16_compat else 0, out.data_ptr(), meta.data_ptr(),
+                                     meta.data_ptr() + 4 * n, cand.data_ptr() if cand is not None else None,
+                                     ws.data_ptr(), ws.numel(), _lib.stream_ptr(device))
+        _lib.check(rc, "f2p_spatial_batched")
+        host = meta.cpu().numpy()     # the one host sync: M' sizes the returned views (spacial_filtering.py:68 syncs too)
+        counts, status = host[:n], host[n:]
+        if (status & 2).any():
+            bad = int((status & 2).nonzero()[0][0])
+            raise IndexError(f"pair {bad}: candidate index out of range of CAD/PC")
+        on_dev = evecs_x.is_cuda
+        flat = out if on_dev else out.to(evecs_x.device)
+        size, M = pk.size, 5 * pk.n2
+        res, infos = [], []
+        for i in range(n):
+            m = int(counts[i])
+            res.append(flat[i * size:i * size + 2 * m].view(2, m))
+            if status[i] & 1 and verbose:
+                print("skipped")  # spacial_filtering.py:70-71
+        if return_info:
+            cflat = cand if on_dev else cand.to(evecs_x.device)
+            for i in range(n):
+                infos.append({"candidates": cflat[i * size:(i + 1) * size].view(2, M), "skipped": bool(status[i] & 1),
+                              "status": int(status[i])})
         return (res, infos) if return_info else res

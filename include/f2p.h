@@ -45,7 +45,7 @@ typedef struct F2PPairDesc {
     int64_t c_off;        /* into C base: [k,k] contiguous                 */
     int64_t cad_off;      /* into CAD base: [ncad,3] contiguous (spatial only) */
     int64_t pc_off;       /* into PC base:  [npc,3] contiguous (spatial only)  */
-    int64_t out_off;      /* into out base: naive [2,n2]; spatial [2,5*n2] (row stride 5*n2) */
+    int64_t out_off;      /* into out base: naive [2,n2]; spatial: 2*5*n2 slots holding the dense [2,M'] result */
     int32_t n1, n2;       /* rows of evecs_x / evecs_y                     */
     int32_t ldx, ldy;     /* row strides of evecs_x / evecs_y in elements  */
     int32_t ncad, npc;    /* rows of CAD / PC (>= n1 / n2; zero-padded rows allowed) */
@@ -71,9 +71,11 @@ int f2p_naive_batched(const float* evecs_x_dev, const float* evecs_y_dev, const 
                       int64_t* out_dev, void* ws_dev, size_t ws_bytes, void* stream);
 
 /* spacial_filtering_fmap2pointmap (spacial_filtering.py:4-75) for a batch of pairs sharing k.
- * out[pair]: int64 [2,5*n2] buffer, survivors in columns [0,M'); counts_dev[pair] = M' (int32);
+ * out[pair]: 2*5*n2 int64 slots; the result is written DENSE as int64 [2,M'] (row stride M') at out_off, so the
+ * caller's tensor is a view of the first 2*M' slots; counts_dev[pair] = M' (int32);
  * status_dev[pair] bit0 = the reference would have printed "skipped" (spacial_filtering.py:70-71).
- * cand_dev (optional, same layout as out) receives nn_query's [2,5*n2] candidates (spacial_filtering.py:22-40). */
+ * cand_dev (optional, 2*5*n2 slots per pair at out_off, row stride 5*n2) receives nn_query's [2,5*n2] candidates
+ * (spacial_filtering.py:22-40). */
 int f2p_spatial_batched(const float* evecs_x_dev, const float* evecs_y_dev, const float* C_dev,
                         const float* cad_dev, const float* pc_dev,
                         const F2PPairDesc* descs_host, int npairs, int k, unsigned flags,
@@ -102,7 +104,8 @@ int f2p_nn_top5(const float* xT_dev, const float* nx_dev, int n1, int ld1,
                 int64_t* idx5_out_dev, void* ws_dev, size_t ws_bytes, void* stream);
 
 /* Kernel 3: spatial-consistency filter (spacial_filtering.py:51-75) on candidate pairs p[2][M] (row stride M).
- * Writes survivors to out[2][M] (row stride M), *count_dev = M', *status_dev bit0 = "skipped";
+ * Writes the survivors dense as int64 [2,M'] (row stride M') into out (2*M slots), *count_dev = M',
+ * *status_dev bit0 = "skipped";
  * mask_dev (optional, uint8 [M]) = 1 for surviving original columns; scores_dev (optional float [3][M]) = the
  * per-round mean |A-B| of the columns alive in that round, in original column positions (others untouched). */
 int f2p_spatial_filter(const float* cad_dev, int ncad, const float* pc_dev, int npc,
@@ -117,7 +120,8 @@ size_t f2p_filter_workspace_bytes(int M);
 
 /* ---- host-buffer convenience (what a non-torch caller binds; copies are inside the call) ------------- */
 
-/* Single pair, HOST pointers in and out; synchronous.  out_host: naive [2,n2]; spatial [2,5*n2] with *count. */
+/* Single pair, HOST pointers in and out; synchronous.  out_host: naive [2,n2]; spatial: 2*5*n2 slots, the first
+ * 2*(*count) hold the dense [2,M'] result. */
 int f2p_naive_host(const float* C_host, const float* evecs_x_host, int n1, const float* evecs_y_host, int n2,
                    int k, unsigned flags, int64_t* out_host);
 int f2p_spatial_host(const float* C_host, const float* evecs_x_host, int n1, const float* evecs_y_host, int n2,

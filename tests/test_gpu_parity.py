@@ -225,7 +225,7 @@ def test_kernel3_vote_scores_bits_and_mask(solvers, oracle, M):
     want, info = oracle.spatial_filter(CAD, PC, p, diam, return_info=True)
     m = int(meta[0])
     assert m == want.shape[1]
-    np.testing.assert_array_equal(out[:, :m].cpu().numpy(), want)
+    np.testing.assert_array_equal(out.flatten()[:2 * m].view(2, m).cpu().numpy(), want)   # dense [2,M']
     assert bool(int(meta[1]) & 1) == info["skipped"]
     keep = np.zeros(M, bool)
     # survivors are a subsequence of the original columns
@@ -309,3 +309,55 @@ def test_top5_overflowing_lists_fall_back_exactly(solvers, oracle, shape):
     torch.cuda.synchronize()
     want = oracle.nn_top5(oracle.project(ex, C), ey)
     np.testing.assert_array_equal(out.cpu().numpy().reshape(n2, 5), want)
+
+
+# ---------------------------------------------------------------------------------------------- stacked batches
+def test_stacked_batch_matches_oracle_and_list_api(solvers, oracle, capsys):
+    """Uniform batch as stacked [P,...] tensors (the no-per-pair-host-work path) vs the oracle and the list API."""
+    from fmap2pointmap_solvers.batched import naive_batched, spatial_batched
+    from fmap2pointmap_solvers.synth import make_pair
+    P = [make_pair(700, 260, 30, seed=900 + i) for i in range(5)]
+    st = lambda name: torch.stack([getattr(p, name) for p in P], 0)   # noqa: E731
+    C, ex, ey, cad, pc = st("C12"), st("evecs_x"), st("evecs_y"), st("CAD"), st("PC")
+    diam = [p.diam_cad * (1.0 + 0.3 * i) for i, p in enumerate(P)]
+    got = naive_batched(C.cuda(), ex.cuda(), ey.cuda())
+    assert tuple(got.shape) == (5, 2, 260) and got.is_cuda
+    for i, p in enumerate(P):
+        np.testing.assert_array_equal(got[i].cpu().numpy(), oracle.naive(p.C12, p.evecs_x, p.evecs_y, int16_compat=False))
+    res = spatial_batched(C.cuda(), ex.cuda(), ey.cuda(), cad.cuda(), pc.cuda(), diam, verbose=False)
+    lst = spatial_batched([p.C12.cuda() for p in P], [p.evecs_x.cuda() for p in P], [p.evecs_y.cuda() for p in P],
+                          [p.CAD.cuda() for p in P], [p.PC.cuda() for p in P], diam, verbose=False)
+    for i, p in enumerate(P):
+        want = oracle.spatial(p.C12, p.evecs_x, p.evecs_y, p.CAD, p.PC, diam[i])
+        np.testing.assert_array_equal(res[i].cpu().numpy(), want)
+        np.testing.assert_array_equal(lst[i].cpu().numpy(), want)
+        assert res[i].is_contiguous() and res[i].dtype == torch.int64
+    # CPU stacked inputs come back on the CPU; a shared C and a shared CAD are broadcast
+    res_cpu = spatial_batched(C[0], ex[:1].expand(5, -1, -1), ey, cad[0], pc, diam, verbose=False)
+    assert not res_cpu[0].is_cuda
+    for i, p in enumerate(P):
+        want = oracle.spatial(P[0].C12, P[0].evecs_x, p.evecs_y, P[0].CAD, p.PC, diam[i])
+        np.testing.assert_array_equal(res_cpu[i].numpy(), want)
+
+
+# ---------------------------------------------------------------------------------------------- host-buffer C-ABI
+def test_host_buffer_entry_points(solvers, oracle):
+    """f2p_naive_host / f2p_spatial_host: what a non-torch caller binds (numpy buffers in and out)."""
+    from fmap2pointmap_solvers import _lib
+    from fmap2pointmap_solvers.batched import thresholds
+    from fmap2pointmap_solvers.synth import make_pair
+    L = _lib.load()
+    p = make_pair(900, 333, 50, seed=31)
+    C, ex, ey, cad, pc = (np.ascontiguousarray(t.numpy()) for t in (p.C12, p.evecs_x, p.evecs_y, p.CAD, p.PC))
+    ptr = lambda a: a.ctypes.data_as(ctypes.c_void_p)   # noqa: E731
+    out = np.zeros((2, 333), np.int64)
+    _lib.check(L.f2p_naive_host(ptr(C), ptr(ex), 900, ptr(ey), 333, 50, 0, ptr(out)), "f2p_naive_host")
+    np.testing.assert_array_equal(out, oracle.naive(p.C12, p.evecs_x, p.evecs_y, int16_compat=False))
+    thr = (ctypes.c_float * 4)(*thresholds(p.diam_cad))
+    buf = np.zeros(10 * 333, np.int64)
+    cnt, st = ctypes.c_int32(0), ctypes.c_int32(0)
+    _lib.check(L.f2p_spatial_host(ptr(C), ptr(ex), 900, ptr(ey), 333, 50, ptr(cad), 900, ptr(pc), 333, thr,
+                                  _lib.F2P_INT16_COMPAT, ptr(buf), ctypes.byref(cnt), ctypes.byref(st)), "f2p_spatial_host")
+    want = oracle.spatial(p.C12, p.evecs_x, p.evecs_y, p.CAD, p.PC, p.diam_cad)
+    assert cnt.value == want.shape[1]
+    np.testing.assert_array_equal(buf[:2 * cnt.value].reshape(2, -1), want)
