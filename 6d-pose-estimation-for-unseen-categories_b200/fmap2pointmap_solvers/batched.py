@@ -224,13 +224,18 @@ def naive_batched(C12: Sequence[torch.Tensor], evecs_x: Sequence[torch.Tensor], 
 
 def spatial_batched(C12: Sequence[torch.Tensor], evecs_x: Sequence[torch.Tensor], evecs_y: Sequence[torch.Tensor],
                     CAD: Sequence[torch.Tensor], PC: Sequence[torch.Tensor], diam_cad: Sequence,
-                    int16_compat: bool = True, return_info: bool = False, verbose: bool = True):
+                    int16_compat: bool = True, return_info: bool = False, verbose: bool = True, packed: bool = False):
     """`spacial_filtering_fmap2pointmap` (spacial_filtering.py:4-75) for a list of pairs sharing K.
+    Stacked 3-D tensors ([P,n,k] ...) select the uniform-batch fast path; there `packed=True` returns
+    (flat int64 [P, 2*5*V2], counts int32 [P], status int32 [P]) on the device WITHOUT a host sync: pair i's dense
+    [2,M'_i] map is `flat[i, :2*counts[i]].view(2, -1)`.
     Returns one int64 [2,M'] tensor per pair (and, with return_info, per-pair dicts with the pre-filter candidates,
     the "skipped" flag and the status word).  The one host sync is the read of the survivor counts."""
     lib = _lib.load()
     if _is_stacked(evecs_x):
-        return _spatial_stacked(lib, C12, evecs_x, evecs_y, CAD, PC, diam_cad, int16_compat, return_info, verbose)
+        return _spatial_stacked(lib, C12, evecs_x, evecs_y, CAD, PC, diam_cad, int16_compat, return_info, verbose, packed)
+    if packed:
+        raise ValueError("packed=True needs a uniform batch given as stacked tensors")
     n = len(evecs_x)
     if n == 0:
         return ([], []) if return_info else []
@@ -295,7 +300,7 @@ def _naive_stacked(lib, C12, evecs_x, evecs_y, int16_compat):
         return res if evecs_x.is_cuda else res.to(evecs_x.device)
 
 
-def _spatial_stacked(lib, C12, evecs_x, evecs_y, CAD, PC, diam_cad, int16_compat, return_info, verbose):
+def _spatial_stacked(lib, C12, evecs_x, evecs_y, CAD, PC, diam_cad, int16_compat, return_info, verbose, packed=False):
     """Uniform batch as stacked tensors.  Returns the list of per-pair int64 [2,M'] maps; each is a VIEW into one
     flat result buffer (no per-pair copy kernels), on the input device."""
     device = _lib.cuda_device_for(evecs_x, evecs_y, C12, CAD, PC)
@@ -303,6 +308,9 @@ def _spatial_stacked(lib, C12, evecs_x, evecs_y, CAD, PC, diam_cad, int16_compat
         pk = _PackedStacked(C12, evecs_x, evecs_y, device, CAD, PC, diam_cad)
         n = pk.n
         if n == 0:
+            if packed:
+                z = torch.zeros(0, dtype=torch.int32, device=device)
+                return torch.empty((0, pk.size), dtype=torch.int64, device=device), z, z
             return ([], []) if return_info else []
         out = torch.empty(max(pk.out_total, 1), dtype=torch.int64, device=device)
         cand = torch.empty(max(pk.out_total, 1), dtype=torch.int64, device=device) if return_info else None
@@ -319,6 +327,8 @@ def _spatial_stacked(lib, C12, evecs_x, evecs_y, CAD, PC, diam_cad, int16_compat
                                      meta.data_ptr() + 4 * n, cand.data_ptr() if cand is not None else None,
                                      ws.data_ptr(), ws.numel(), _lib.stream_ptr(device))
         _lib.check(rc, "f2p_spatial_batched")
+        if packed:
+            return out.view(n, pk.size), meta[:n], meta[n:]
         host = meta.cpu().numpy()     # the one host sync: M' sizes the returned views (spacial_filtering.py:68 syncs too)
         counts, status = host[:n], host[n:]
         if (status & 2).any():

@@ -216,21 +216,22 @@ def run_b200_arm(args, wl):
         return naive_batched(src["C"], src["ex"], src["ey"])
 
     def step_resident():
-        return solve(devt)
+        # device-resident, asynchronous form of the call: spatial returns (flat maps, counts, status) with no host sync
+        if spatial:
+            return spatial_batched(devt["C"], devt["ex"], devt["ey"], devt["cad"], devt["pc"], diam, verbose=False, packed=True)
+        return naive_batched(devt["C"], devt["ex"], devt["ey"])
 
     def gather_maps(out):
-        # return the index maps to every rank: one NCCL all-gather over NVLink (payload padded to the max size)
+        # return the index maps to every rank: NCCL all-gather over NVLink of the rank's result buffer (+ counts)
         if dist is None:
             return
-        if spatial:
-            flat = torch.full((ppg, 2, 5 * n2), -1, dtype=torch.int64, device=dev)
-            for i, o in enumerate(out):
-                flat[i, :, :o.shape[1]] = o
-        else:
-            flat = out
-        allm = torch.empty((world,) + tuple(flat.shape), dtype=flat.dtype, device=dev)
-        dist.all_gather_into_tensor(allm, flat)
-        return allm
+        parts = list(out[:2]) if spatial else [out]
+        res = []
+        for t in parts:
+            allm = torch.empty((world,) + tuple(t.shape), dtype=t.dtype, device=dev)
+            dist.all_gather_into_tensor(allm, t.contiguous())
+            res.append(allm)
+        return res
 
     d2h_bytes = [0]
 
