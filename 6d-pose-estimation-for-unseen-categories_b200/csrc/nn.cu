@@ -387,7 +387,7 @@ __device__ __forceinline__ void gated_compact(int col, float* s_val, uint32_t* s
     if (m == K) s_tau[col] = raw[K - 1];
 }
 
-template <int K, int KC, int NSTAGE>
+template <int K, int KC, int NSTAGE, int NXP>   // NXP: L1 prefetch of the row norms at tile start, load in the epilogue
 __global__ void __launch_bounds__(NN_THREADS, 2)
 nn_gated_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapY, const NNParams prm) {
     constexpr int CAP = GatedCfg<K>::CAP;
@@ -408,6 +408,9 @@ nn_gated_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
     u64* s_best = reinterpret_cast<u64*>(s_cnt);                     // K == 1: [TILE] exact keys (lists unused)
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // Lane layout: half-warp = 2 (row groups) x 8 (column groups).  Tried and measured slower on B200: 16 x 2 with
+    // warp-private columns (8 instead of 12 shared-memory wavefronts per k-step, tools/lds_pattern.cu) — arg-min
+    // 46.0 vs 44.7 ms at 100k x 100k x 128, top-5 3.9 vs 3.1 ms at 50k x 20k x 50.
     const int tx = ((warp & 1) << 3) | (lane & 7);
     const int ty = ((warp >> 1) << 2) | ((lane >> 4) << 1) | ((lane >> 3) & 1);
 
@@ -466,8 +469,16 @@ nn_gated_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
     int s = 0;
     for (int t = 0; t < ntiles; ++t) {
         const int rowbase = (t_begin + t) * TILE;
-        const float4 nxa = __ldg(reinterpret_cast<const float4*>(prm.nx + xcol + rowbase + ty * 4));
-        const float4 nxb = __ldg(reinterpret_cast<const float4*>(prm.nx + xcol + rowbase + 64 + ty * 4));
+        // row norms: pulled into L1 now, loaded in the epilogue (ptxas sinks a plain early load down to its use to save
+        // registers, where it then costs an L2 round trip per tile)
+        float4 nxa, nxb;
+        if (NXP) {
+            prefetch_l1(prm.nx + xcol + rowbase + ty * 4);
+            prefetch_l1(prm.nx + xcol + rowbase + 64 + ty * 4);
+        } else {
+            nxa = __ldg(reinterpret_cast<const float4*>(prm.nx + xcol + rowbase + ty * 4));
+            nxb = __ldg(reinterpret_cast<const float4*>(prm.nx + xcol + rowbase + 64 + ty * 4));
+        }
         u64 acc[8][4];
 #pragma unroll
         for (int i = 0; i < 8; ++i)
@@ -510,6 +521,10 @@ nn_gated_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
             if (lane == 0) mbar_arrive(&empty[slot]);
         }
 
+        if (NXP) {
+            nxa = __ldg(reinterpret_cast<const float4*>(prm.nx + xcol + rowbase + ty * 4));
+            nxb = __ldg(reinterpret_cast<const float4*>(prm.nx + xcol + rowbase + 64 + ty * 4));
+        }
         const float nxv[8] = {nxa.x, nxa.y, nxa.z, nxa.w, nxb.x, nxb.y, nxb.z, nxb.w};
         // row i of this thread: values (acc + nx) + ny for its 8 columns, gate against tau, append the rare passes
         auto gate_row = [&](int i) {
@@ -552,8 +567,7 @@ nn_gated_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
         if (t == 0) {
             // bootstrap (tau = +inf): bounded appends per cut so the first tile cannot overflow
             if (K == 1) {
-                // exact local arg-min over this thread's 8 rows, merged across the 4 lanes sharing a column:
-                // at most 4 entries per column
+                // exact local arg-min over this thread's 8 rows, merged across the 4 lanes sharing a column
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     float bd = INF, braw = INF; uint32_t bi = IDX_NONE;
@@ -580,7 +594,7 @@ nn_gated_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
                         gated_best1(j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4), braw, wi, s_tau, s_best);
                 }
             } else {
-                // one row of every thread per cut: at most 16 appends per column on top of the K kept
+                // one row of every lane per cut: at most 16 appends per column on top of the K kept
                 for (int step_i = 0; step_i < 8; ++step_i) {
 #pragma unroll
                     for (int i = 0; i < 8; ++i)
@@ -600,7 +614,10 @@ nn_gated_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
         } else {
 #pragma unroll
             for (int i = 0; i < 8; ++i) gate_row(i);
-            if (K != 1) cut_and_reload();        // K == 1 runs without any CTA-wide synchronisation
+            // K == 1 runs without any CTA-wide synchronisation.  K == 5 cuts (two CTA barriers) after every tile while
+            // the threshold is loose, then after every 2nd / 4th tile: the appends of an interval of n rows after r
+            // seen rows exceed m with probability ~ C(m+4,4) (n/(r+n))^m, < 1e-9 for m = CAP - K at n/(r+n) <= 1/3.
+            if (K != 1 && (t < 4 || t == ntiles - 1 || (t < 8 ? (t & 1) == 1 : (t & 3) == 3))) cut_and_reload();
         }
     }
 
@@ -772,23 +789,34 @@ static int launch_mode(const float* xT, int64_t ld1_total, const float* yT, int6
 }
 
 template <int K>
-static size_t gated_smem_bytes(int k) {
-    const int nkc = (k + KC - 1) / KC;
-    return ((size_t)nkc * KC * TILE + (size_t)NSTAGE * KC * TILE) * sizeof(float) + 16 * sizeof(uint64_t) +
+static size_t gated_smem_bytes(int k, int kc, int nstage) {
+    const int nkc = (k + kc - 1) / kc;
+    return ((size_t)nkc * kc * TILE + (size_t)nstage * kc * TILE) * sizeof(float) + 16 * sizeof(uint64_t) +
            2 * TILE * sizeof(int) + (size_t)GatedCfg<K>::CAP * TILE * 8 + 16;
 }
 
 template <int K>
 static int launch_gated(const float* xT, int64_t ld1_total, const float* yT, int64_t ld2_total, int k, const NNParams& prm,
                         int total_items, cudaStream_t stream) {
+    const char* ek = getenv("F2P_GATED_KC");
+    const int kcv = ek ? atoi(ek) : KC;
     CUtensorMap mapX, mapY;
     int rc = make_tensor_map_2d(&mapX, xT, (uint64_t)ld1_total, (uint64_t)k, (uint64_t)ld1_total, TILE, KC);
     if (rc) return rc;
     rc = make_tensor_map_2d(&mapY, yT, (uint64_t)ld2_total, (uint64_t)k, (uint64_t)ld2_total, TILE, KC);
     if (rc) return rc;
-    const size_t smem = gated_smem_bytes<K>(k);
-    F2P_CUDA(cudaFuncSetAttribute(nn_gated_kernel<K, KC, NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    nn_gated_kernel<K, KC, NSTAGE><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);
+    // Row-norm L1 prefetch: +2 % for the arg-min kernel at 100k x 100k x 128, slightly negative for top-5 (registers).
+    // F2P_GATED_NXP overrides (tools/nn_time.py).
+    const char* ep = getenv("F2P_GATED_NXP");
+    const int nxp = ep ? atoi(ep) : (K == 1 ? 1 : 0);
+    const size_t smem = gated_smem_bytes<K>(k, KC, NSTAGE);
+    if (nxp) {
+        F2P_CUDA(cudaFuncSetAttribute(nn_gated_kernel<K, KC, NSTAGE, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        nn_gated_kernel<K, KC, NSTAGE, 1><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);
+    } else {
+        F2P_CUDA(cudaFuncSetAttribute(nn_gated_kernel<K, KC, NSTAGE, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        nn_gated_kernel<K, KC, NSTAGE, 0><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);
+    }
     F2P_CUDA(cudaGetLastError());
     return 0;
 }
