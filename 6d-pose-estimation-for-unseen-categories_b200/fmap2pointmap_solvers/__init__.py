@@ -4,12 +4,14 @@
 
 exposes the same three callables with the same signatures and return contract; underneath, Python/PyTorch host code
 calls hand-written sm_100a CUDA kernels through the C-ABI of libf2p_sm100.so (include/f2p.h).  There is no CPU
-fallback.  Batched and multi-GPU entry points are additions (`naive_batched`, `spatial_batched`, `distributed`).
+fallback.  Batched and multi-GPU entry points are additions (`naive_batched`, `spatial_batched`, `distributed`), as is the
+batched form of the inlier ratio that `scripts/eval.py:88` computes right after the solver (`inlier`).
 """
 from ._gin import configurable as _configurable
 from .spacial_filtering import spacial_filtering_fmap2pointmap
 from .naive import naive_fmap2pointmap
 from .batched import naive_batched, spatial_batched
+from .inlier import compute_inlier_ratio, inlier_ratio_batched
 
 
 @_configurable
@@ -19,4 +21,4 @@ def choose_fmap2pointmap_solver(solver):
 
 
 __all__ = ["naive_fmap2pointmap", "spacial_filtering_fmap2pointmap", "choose_fmap2pointmap_solver",
-           "naive_batched", "spatial_batched"]
+           "naive_batched", "spatial_batched", "compute_inlier_ratio", "inlier_ratio_batched"]

@@ -56,6 +56,10 @@ _SIGNATURES = {
     "f2p_spatial_host": (ctypes.c_int, [_c_vp, _c_vp, ctypes.c_int, _c_vp, ctypes.c_int, ctypes.c_int, _c_vp, ctypes.c_int,
                                         _c_vp, ctypes.c_int, ctypes.POINTER(ctypes.c_float), ctypes.c_uint, _c_vp,
                                         ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]),
+    "f2p_inlier_ratio_batched": (ctypes.c_int, [_c_vp, _c_vp, _c_vp, ctypes.POINTER(F2PPairDesc), ctypes.c_int, ctypes.c_int,
+                                                _c_vp, ctypes.POINTER(ctypes.c_float), _c_vp, _c_vp, _c_vp,
+                                                ctypes.c_size_t, _c_vp]),
+    "f2p_inlier_workspace_bytes": (ctypes.c_size_t, [ctypes.c_int]),
     "f2p_measure_fp32_peak": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), _c_vp]),
 }
 

@@ -347,6 +347,19 @@ def _event_time(fn, reps, warmup, flush):
     return sum(ts) / len(ts), ts[0]
 
 
+def _traffic(wl):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu capture of this workload (None when the
+    workload has no capture)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+            t = json.load(f)
+    except Exception:
+        return None
+    if wl["n1"] == 100_000 and wl["k"] == 128 and wl["solver"] == "naive":
+        return t.get("large", {}).get("bytes")
+    return None
+
+
 def roofline_section(L, _lib, wl, dev):
     """Per-kernel rooflines measured live with CUDA events on the launching (current) stream.
     Dominant kernel = kernel 2 (fused distance + argmin/top-5): FP32-pipe bound, algorithmic flops 2*n1*n2*k."""
@@ -400,7 +413,7 @@ def roofline_section(L, _lib, wl, dev):
         "peak_scalar_ffma": scalar.value,
         "algorithmic_flops_per_launch": flops, "ms_per_launch": nm, "ms_best": nb,
         "timed": "CUDA events on the launching stream around f2p_nn_%s (key fill + fused kernel + index finalise)" % ("top5" if top5 else "argmin"),
-        "traffic": None,
+        "traffic": _traffic(wl),
         "projection": {"bound": "hbm", "achieved": proj_bytes / (pm * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                        "frac": proj_bytes / (pm * 1e-3) / 1e9 / hbm_peak, "ms_per_launch": pm,
                        "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650 GB/s",

@@ -118,6 +118,19 @@ size_t f2p_project_workspace_bytes(void);
 size_t f2p_nn_workspace_bytes(int n1, int n2, int k, int top5);
 size_t f2p_filter_workspace_bytes(int M);
 
+/* ---- inlier ratio of the predicted maps (utils/utils.py:81-105, called per sample at scripts/eval.py:88) ---- */
+
+/* For pair i and every column c < M_i of its dense int64 [2,M_i] map at maps_dev + descs[i].out_off (M_i = n2 for
+ * naive maps; counts_dev[i] when spatial != 0): inlier iff sqrt(|CAD[p0] - PC_aligned[p1]|^2) < thr_host[i], with
+ * CAD at cad_dev + cad_off ([ncad,3]) and the ground-truth-aligned cloud at pc_aligned_dev + pc_off ([npc,3]).
+ * inliers_dev[i] = count (int32; -1 when an index is out of range), ratio_dev[i] (optional) = fp32(count)/fp32(M_i),
+ * 0 when M_i == 0 (the reference returns 0 for an empty map).  Negative indices wrap once, as torch indexing does. */
+int f2p_inlier_ratio_batched(const float* cad_dev, const float* pc_aligned_dev, const int64_t* maps_dev,
+                             const F2PPairDesc* descs_host, int npairs, int spatial, const int32_t* counts_dev,
+                             const float* thr_host, int32_t* inliers_dev, float* ratio_dev,
+                             void* ws_dev, size_t ws_bytes, void* stream);
+size_t f2p_inlier_workspace_bytes(int npairs);
+
 /* ---- host-buffer convenience (what a non-torch caller binds; copies are inside the call) ------------- */
 
 /* Single pair, HOST pointers in and out; synchronous.  out_host: naive [2,n2]; spatial: 2*5*n2 slots, the first

@@ -414,3 +414,23 @@ F2PO_API int64_t f2po_spatial(const float* C, const float* evecs_x, int64_t n1, 
     free(feat); free(idx5); free(p);
     return m;
 }
+
+/* ---- inlier ratio ------------------------------------------------------------------------------------
+ * compute_inlier_ratio (utils/utils.py:81-105): CAD[pred[:,0]], PC_aligned[pred[:,1]] (torch indexing: negative
+ * indices wrap once), sq = square(a-b).sum(-1) [((q0+q1)+q2), FP32], dist = sq ** 0.5 [sqrt; IEEE here, see the
+ * header note on MKL's vsSqrt], inliers = (dist < thr).sum().  Returns the count, or -1 on an out-of-range index. */
+F2PO_API int64_t f2po_inlier_count(const float* CAD, int64_t ncad, const float* PC, int64_t npc,
+                                   const int64_t* p0, const int64_t* p1, int64_t M, float thr) {
+    int64_t n = 0;
+    for (int64_t c = 0; c < M; ++c) {
+        int64_t i = p0[c], j = p1[c];
+        if (i < 0) i += ncad;
+        if (j < 0) j += npc;
+        if (i < 0 || i >= ncad || j < 0 || j >= npc) return -1;
+        const float dx = CAD[3 * i] - PC[3 * j], dy = CAD[3 * i + 1] - PC[3 * j + 1], dz = CAD[3 * i + 2] - PC[3 * j + 2];
+        const float qx = dx * dx, qy = dy * dy, qz = dz * dz;
+        const float s = (qx + qy) + qz;
+        if (sqrtf(s) < thr) ++n;
+    }
+    return n;
+}

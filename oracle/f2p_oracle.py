@@ -60,6 +60,8 @@ def lib():
         L.f2po_spatial.argtypes = [_f32p, _f32p, _i64, _f32p, _i64, _int, _f32p, _i64, _f32p, _i64, _f32p,
                                    _int, _i64p, _i64p, _i64p, _i32p]
         L.f2po_spatial.restype = _i64
+        L.f2po_inlier_count.argtypes = [_f32p, _i64, _f32p, _i64, _i64p, _i64p, _i64, ctypes.c_float]
+        L.f2po_inlier_count.restype = _i64
         _lib = L
     return _lib
 
@@ -194,3 +196,19 @@ def spatial(C12, evecs_x, evecs_y, CAD, PC, diam_cad, int16_compat=True, return_
         return res, {"round_counts": rounds, "skipped": bool(skipped.value),
                      "candidates": np.ascontiguousarray(cand.reshape(-1)[: 2 * K * n2].reshape(2, K * n2))}
     return res
+
+
+def inlier_ratio(pred_corr, CAD, PC_aligned, threshold):
+    """compute_inlier_ratio (utils/utils.py:81-105) on a [M,2] (or [2,M] transposed by the caller) index array:
+    returns (ratio as np.float32 — 0 for an empty map —, inlier count)."""
+    pc = np.ascontiguousarray(np.asarray(pred_corr, np.int64))
+    M = pc.shape[0]
+    if M == 0:
+        return np.float32(0), 0
+    p0 = np.ascontiguousarray(pc[:, 0]); p1 = np.ascontiguousarray(pc[:, 1])
+    cad = _f32(CAD); pca = _f32(PC_aligned)
+    thr = float(np.float32(float(threshold)))
+    n = lib().f2po_inlier_count(_fp(cad), cad.shape[0], _fp(pca), pca.shape[0], _ip(p0), _ip(p1), M, thr)
+    if n < 0:
+        raise IndexError("correspondence index out of range")
+    return np.float32(n) / np.float32(M), int(n)

@@ -10,6 +10,8 @@ oracle/ref_loader.py) is run on CPU and its outputs are stored together with a d
   <case>/diam          float64        the diam_cad actually used
   <case>/digest        str            sha256 of the inputs
   <case>/skipped       bool           whether the reference printed "skipped" (spacial_filtering.py:70-71)
+  <case>/ir            float32        utils.compute_inlier_ratio(p_pred.t(), CAD, aligned_pc, 0.1*diam) (utils/utils.py:81-105,
+                                      as called at scripts/eval.py:88); 0 for an empty map
 """
 import contextlib
 import io
@@ -26,7 +28,8 @@ sys.path.insert(0, os.path.join(ROOT, "6d-pose-estimation-for-unseen-categories_
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 from oracle.ref_loader import load_reference  # noqa: E402
-from golden.cases import CASES, build_inputs, inputs_digest  # noqa: E402
+from golden.cases import CASES, aligned_pc, build_inputs, inputs_digest, ir_threshold  # noqa: E402
+from oracle.ref_loader import load_reference_utils  # noqa: E402
 
 
 def _find_fallback_diam(ref, inp):
@@ -51,6 +54,7 @@ def _find_fallback_diam(ref, inp):
 
 def main():
     ref = load_reference()
+    ref_utils = load_reference_utils()
     torch.manual_seed(0)
     out = {}
     meta = {"torch": torch.__version__, "threads": torch.get_num_threads(), "cases": {}}
@@ -71,6 +75,9 @@ def main():
         out[name + "/diam"] = np.float64(float(inp["diam_cad"]))
         out[name + "/digest"] = np.array(inputs_digest(inp))
         out[name + "/skipped"] = np.array("skipped" in buf.getvalue())
+        if p.shape[1] == 0 or int(p[1].max()) < inp["PC"].shape[0]:
+            ir = ref_utils.compute_inlier_ratio(p.t(), inp["CAD"], aligned_pc(name, inp), ir_threshold(inp))
+            out[name + "/ir"] = np.float32(float(ir))
         C2 = inp["C12"].squeeze(0) if inp["C12"].dim() == 3 else inp["C12"]
         feat = torch.matmul(inp["evecs_x"], C2.t())
         if c["kind"] == "spatial":

@@ -58,3 +58,22 @@ def load_reference():
         sys.modules["_f2p_reference." + k] = v
     assert os.path.realpath(mod.__file__).startswith(os.path.realpath(REFERENCE_ROOT)), mod.__file__
     return mod
+
+
+def load_reference_utils():
+    """The reference's `utils/utils.py` module object (compute_inlier_ratio, C_from_sparse_P, ...), unmodified."""
+    import importlib.util
+    path = os.path.join(REFERENCE_ROOT, "utils", "utils.py")
+    if not os.path.isfile(path):
+        raise RuntimeError(f"reference utils not found under {REFERENCE_ROOT}")
+    saved_gin = sys.modules.get("gin")
+    if saved_gin is None:
+        sys.modules["gin"] = _gin_shim()
+    try:
+        spec = importlib.util.spec_from_file_location("_f2p_reference.utils_utils", path)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+    finally:
+        if saved_gin is None:
+            del sys.modules["gin"]
+    return mod

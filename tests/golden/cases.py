@@ -76,3 +76,26 @@ def inputs_digest(inp) -> str:
     d = inp["diam_cad"]
     h.update(np.float64(float(d)).tobytes())
     return h.hexdigest()
+
+
+def aligned_pc(name, inp):
+    """The scene cloud under the ground-truth pose for the inlier-ratio cases (`Obj["align_pc"]`, scripts/eval.py:88):
+    CAD[gt] plus a small seeded jitter for scene points with a ground-truth CAD vertex, the raw scene point otherwise."""
+    c = CASES[name]
+    P = make_pair(c["n1"], c["n2"], c["k"], seed=c["seed"])
+    g = torch.Generator().manual_seed(c["seed"] + 777)
+    n2 = c["n2"]
+    CAD, PC = inp["CAD"], inp["PC"]
+    out = PC.clone()
+    has = P.perm >= 0
+    gt = P.perm.clamp_min(0)
+    if c.get("dup_rows"):
+        gt = gt % (c["n1"] // 2)
+    jitter = 1.1 * torch.randn(n2, 3, generator=g)      # distances spread around the 0.1*diam threshold
+    out[:n2][has] = (CAD[gt] + jitter)[has]
+    return out.contiguous()
+
+
+def ir_threshold(inp):
+    """0.1 * diam_cad exactly as scripts/eval.py:88 forms it (host-language product for numbers, tensor op for tensors)."""
+    return 0.1 * inp["diam_cad"]

@@ -361,3 +361,68 @@ def test_host_buffer_entry_points(solvers, oracle):
     want = oracle.spatial(p.C12, p.evecs_x, p.evecs_y, p.CAD, p.PC, p.diam_cad)
     assert cnt.value == want.shape[1]
     np.testing.assert_array_equal(buf[:2 * cnt.value].reshape(2, -1), want)
+
+
+# ---------------------------------------------------------------------------------------------- BASELINE cfg5 sweep
+@pytest.mark.parametrize("k", [30, 64, 128])
+@pytest.mark.parametrize("n1", [2000, 10000, 50000])
+def test_cfg5_sweep_both_solvers_vs_oracle(solvers, oracle, n1, k):
+    """BASELINE.json configs[4]: n1 in {2k,10k,50k} x k in {30,64,128}, n2 = 2000, both solvers, bit-exact vs the oracle."""
+    from fmap2pointmap_solvers.synth import make_pair
+    p = make_pair(n1, 2000, k, seed=5000 + n1 + k)
+    C, ex, ey, cad, pc = (t.cuda() for t in (p.C12, p.evecs_x, p.evecs_y, p.CAD, p.PC))
+    got = solvers.naive_fmap2pointmap(C, ex, ey).cpu().numpy()
+    np.testing.assert_array_equal(got, oracle.naive(p.C12, p.evecs_x, p.evecs_y, int16_compat=False))
+    for scale in (1.0, 2.5):       # 2.5: looser thresholds, so every round keeps a few thousand candidates
+        got = solvers.spacial_filtering_fmap2pointmap(C, ex, ey, CAD=cad, PC=pc, diam_cad=p.diam_cad * scale).cpu().numpy()
+        np.testing.assert_array_equal(got, oracle.spatial(p.C12, p.evecs_x, p.evecs_y, p.CAD, p.PC, p.diam_cad * scale))
+
+
+# ---------------------------------------------------------------------------------------------- inlier ratio
+@pytest.mark.parametrize("name", list(CASES))
+def test_inlier_ratio_matches_reference_golden(solvers, golden, name):
+    """compute_inlier_ratio (drop-in for utils/utils.py:81-105) on the reference's own maps vs the reference's ratio."""
+    from fmap2pointmap_solvers import compute_inlier_ratio
+    from golden.cases import aligned_pc, ir_threshold
+    c, inp = load_case(golden, name)
+    p = torch.from_numpy(golden[name + "/p_pred"])
+    got = compute_inlier_ratio(p.t().cuda(), inp["CAD"].cuda(), aligned_pc(name, inp).cuda(), ir_threshold(inp))
+    want = np.float32(golden[name + "/ir"])
+    if p.shape[1] == 0:
+        assert got == 0 and isinstance(got, int)
+    else:
+        assert got.is_cuda and got.dtype == torch.float32 and got.dim() == 0
+        assert np.float32(got.item()).view(np.int32) == want.view(np.int32)
+    # CPU tensors in -> CPU scalar out
+    got_cpu = compute_inlier_ratio(p.t(), inp["CAD"], aligned_pc(name, inp), ir_threshold(inp))
+    assert float(got_cpu) == float(want)
+
+
+def test_inlier_ratio_batched_on_solver_output(solvers, oracle):
+    """Solver output -> inlier ratios without leaving the device: naive [P,2,V2] maps and the packed spatial buffer."""
+    from fmap2pointmap_solvers import inlier_ratio_batched
+    from fmap2pointmap_solvers.batched import naive_batched, spatial_batched
+    from fmap2pointmap_solvers.synth import make_pair
+    P = [make_pair(900, 300, 30, seed=700 + i) for i in range(4)]
+    st = lambda name: torch.stack([getattr(p, name) for p in P], 0).cuda()   # noqa: E731
+    C, ex, ey, cad, pc = st("C12"), st("evecs_x"), st("evecs_y"), st("CAD"), st("PC")
+    g = torch.Generator().manual_seed(1)
+    aligned = torch.stack([p.CAD[p.perm.clamp_min(0)] + 1.0 * torch.randn(300, 3, generator=g) for p in P], 0)
+    thr = [0.1 * p.diam_cad for p in P]
+    maps = naive_batched(C, ex, ey)
+    got = inlier_ratio_batched(maps, cad, aligned.cuda(), thr).cpu().numpy()
+    for i, p in enumerate(P):
+        want, _ = oracle.inlier_ratio(maps[i].t().cpu().numpy(), p.CAD, aligned[i], thr[i])
+        assert got[i].view(np.int32) == np.float32(want).view(np.int32)
+    diam = [p.diam_cad * 2.0 for p in P]
+    flat, counts, status = spatial_batched(C, ex, ey, cad, pc, diam, verbose=False, packed=True)
+    got = inlier_ratio_batched(flat, cad, aligned.cuda(), thr, counts=counts).cpu().numpy()
+    cnt = counts.cpu().numpy()
+    assert cnt.max() > 0
+    for i, p in enumerate(P):
+        m = flat[i, :2 * cnt[i]].view(2, -1)
+        want, _ = oracle.inlier_ratio(m.t().cpu().numpy(), p.CAD, aligned[i], thr[i])
+        assert got[i].view(np.int32) == np.float32(want).view(np.int32)
+    with pytest.raises(IndexError):
+        from fmap2pointmap_solvers import compute_inlier_ratio
+        compute_inlier_ratio(torch.tensor([[0, 5000]]).cuda(), cad[0], aligned[0].cuda(), 1.0)

@@ -112,3 +112,35 @@ def test_c_oracle_matches_live_reference(shape):
     np.testing.assert_array_equal(O.naive(P.C12, P.evecs_x, P.evecs_y), want)
     want = ref.spacial_filtering_fmap2pointmap(P.C12, P.evecs_x, P.evecs_y, P.CAD, P.PC, P.diam_cad).numpy()
     np.testing.assert_array_equal(O.spatial(P.C12, P.evecs_x, P.evecs_y, P.CAD, P.PC, P.diam_cad), want)
+
+
+# ---------------------------------------------------------------------------------------------- inlier ratio
+ALL_IR = [n for n in CASES]
+
+
+@pytest.mark.parametrize("name", ALL_IR)
+def test_oracle_inlier_ratio_matches_reference_golden(golden, name):
+    """oracle.inlier_ratio vs utils.compute_inlier_ratio of the real reference (stored by oracle/make_golden.py)."""
+    from golden.cases import aligned_pc, ir_threshold
+    from oracle import f2p_oracle as O
+    c, inp = load_case(golden, name)
+    p = golden[name + "/p_pred"]
+    ratio, _ = O.inlier_ratio(p.T, inp["CAD"], aligned_pc(name, inp), ir_threshold(inp))
+    assert np.float32(ratio).view(np.int32) == np.float32(golden[name + "/ir"]).view(np.int32)
+
+
+@pytest.mark.skipif(not reference_available(), reason="/root/reference only exists in the build container")
+def test_oracle_inlier_ratio_matches_live_reference():
+    from oracle import f2p_oracle as O
+    from oracle.ref_loader import load_reference_utils
+    ru = load_reference_utils()
+    g = torch.Generator().manual_seed(3)
+    CAD = torch.rand(4000, 3, generator=g) * 10
+    PCa = torch.rand(3000, 3, generator=g) * 10
+    corr = torch.stack([torch.randint(0, 4000, (20000,), generator=g), torch.randint(-3000, 3000, (20000,), generator=g)], 1)
+    PCa[corr[:5000, 1]] = CAD[corr[:5000, 0]] + 0.9 * torch.randn(5000, 3, generator=g)
+    for thr in (1.73, np.float64(0.931), torch.tensor(2.2)):
+        want = ru.compute_inlier_ratio(corr, CAD, PCa, thr)
+        got, _ = O.inlier_ratio(corr.numpy(), CAD, PCa, float(thr))
+        assert np.float32(float(want)).view(np.int32) == np.float32(got).view(np.int32)
+    assert ru.compute_inlier_ratio(corr[:0], CAD, PCa, 1.0) == 0 and O.inlier_ratio(corr[:0].numpy(), CAD, PCa, 1.0)[0] == 0
