@@ -47,6 +47,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--pairs-per-gpu", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the cfg2 / cfg3 side measurements of the default run")
     return ap.parse_args()
 
 
@@ -318,6 +319,8 @@ def run_b200_arm(args, wl):
     # spatial: gated top-5 + exact fallback + finalise 3, filter init + 3 x (vote + combine) 7)
     line["gpu_launches"] = (14 if spatial else 7) * args.steps
 
+    if rank == 0 and world == 1 and args.workload == "large" and not args.no_extra:
+        line["other_workloads"] = side_workloads()
     if rank == 0:
         line["roofline"] = roofline_section(L, _lib, wl, dev)
         if not args.no_cpu_baseline:
@@ -331,6 +334,23 @@ def run_b200_arm(args, wl):
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def side_workloads():
+    """The pairs/s half of BASELINE.json's metric: cfg2 (one 5k x 2k x 50 pair, naive) and cfg3 (256 pairs with the
+    spatial filter) measured by this same script in a child process each, reported beside the cfg4 headline."""
+    out = {}
+    for name, extra in (("pair", ["--steps", "50", "--warmup", "5"]), ("batch", ["--steps", "5", "--warmup", "3"])):
+        try:
+            r = subprocess.run([sys.executable, os.path.abspath(__file__), "--workload", name, "--no-cpu-baseline"] + extra,
+                               capture_output=True, text=True, timeout=600)
+            d = json.loads(r.stdout.strip().splitlines()[-1])
+            out[name] = {"workload": d["config"]["workload"], "pairs_per_s": d["pairs_per_s"], "ms_per_step": d["ms_per_step"],
+                         "value": d["value"], "unit": d["unit"], "e2e_pairs_per_s": d["e2e"]["pairs_per_s"],
+                         "kernel2_tflops": d["roofline"]["achieved"]}
+        except Exception as e:   # a side measurement must never cost the headline line
+            out[name] = {"error": repr(e)[:200]}
+    return out
 
 
 def _event_time(fn, reps, warmup, flush):

@@ -114,3 +114,27 @@ def test_pair_sharding_allgather_gloo_world2():
     for p in procs:
         p.join(timeout=60)
     assert sorted(results) == [(0, True), (1, True)]
+
+
+def test_result_files_roundtrip_in_reference_layout(tmp_path):
+    """`.pt` hand-off (scripts/eval.py:104-119 writer, scripts/test_RANSAC.py:331-376 reader)."""
+    from fmap2pointmap_solvers import results_io as R
+    samples = []
+    for i in range(3):
+        samples.append([{"xyz": torch.rand(10, 3)}, {"xyz": torch.rand(7, 3)},
+                        {"obj_id": 5 + i, "P": torch.zeros(4, 2, dtype=torch.int64), "diam_cad": 17.0}])
+    p = [torch.randint(0, 7, (2, 4 + i)) for i in range(3)]
+    C = torch.rand(3, 30, 30)
+    irs = [torch.tensor(0.5), 0, torch.tensor(1.0)]
+    R.attach_results(samples, p, C, irs)
+    paths = R.save_results(samples, str(tmp_path), start_idx=10)
+    assert [os.path.basename(q) for q in paths] == ["10_obj_5.pt", "11_obj_6.pt", "12_obj_7.pt"]
+    back = R.load_results(str(tmp_path))
+    assert len(back) == 3
+    for i, r in enumerate(back):
+        P_pred, cad_xyz, ir, obj_id = R.correspondences(r)
+        assert P_pred.shape == (4 + i, 2) and obj_id == 5 + i
+        np.testing.assert_array_equal(P_pred, p[i].T.numpy())
+        assert torch.equal(r[-1]["C_pred"], C[i]) and torch.equal(cad_xyz, samples[i][0]["xyz"])
+    with pytest.raises(ValueError):
+        R.attach_results(samples, [t.float() for t in p], C, irs)
