@@ -60,6 +60,11 @@ _SIGNATURES = {
                                                 _c_vp, ctypes.POINTER(ctypes.c_float), _c_vp, _c_vp, _c_vp,
                                                 ctypes.c_size_t, _c_vp]),
     "f2p_inlier_workspace_bytes": (ctypes.c_size_t, [ctypes.c_int]),
+    "f2p_find_positives_count": (ctypes.c_int, [_c_vp, ctypes.c_int, _c_vp, ctypes.c_int, ctypes.c_int, ctypes.c_double,
+                                                _c_vp, _c_vp, _c_vp, _c_vp, ctypes.c_size_t, _c_vp]),
+    "f2p_find_positives_write": (ctypes.c_int, [_c_vp, ctypes.c_int, _c_vp, ctypes.c_int, ctypes.c_int, ctypes.c_double,
+                                                _c_vp, ctypes.c_int64, _c_vp, ctypes.c_size_t, _c_vp]),
+    "f2p_positives_workspace_bytes": (ctypes.c_size_t, [ctypes.c_int]),
     "f2p_measure_fp32_peak": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), _c_vp]),
 }
 

@@ -131,6 +131,20 @@ int f2p_inlier_ratio_batched(const float* cad_dev, const float* pc_aligned_dev, 
                              void* ws_dev, size_t ws_bytes, void* stream);
 size_t f2p_inlier_workspace_bytes(int npairs);
 
+/* ---- ground-truth correspondences of a sample (dataset/object.py:281-288 find_positives, :311-317 get_overlap) ---- */
+
+/* All (i,j) with sqrt(((d0^2+d1^2)+d2^2)) <= r between pc1 [n1,3] and pc2 [n2,3] (both float64 when is_f64 != 0, else
+ * float32; the arithmetic runs in that type, r is cast to it), in row-major order.
+ * Pass 1 `_count`: *total_dev = N (int64), overlap12_dev[i] / overlap21_dev[j] (optional int8) = 1 when row i /
+ * column j has a positive; the per-row offsets stay in the workspace.  Pass 2 `_write` (same arguments and workspace,
+ * after the caller sized pairs_dev from N): pairs_dev int64 [N,2], at most `capacity` pairs are written. */
+int f2p_find_positives_count(const void* pc1_dev, int n1, const void* pc2_dev, int n2, int is_f64, double r,
+                             int64_t* total_dev, int8_t* overlap12_dev, int8_t* overlap21_dev,
+                             void* ws_dev, size_t ws_bytes, void* stream);
+int f2p_find_positives_write(const void* pc1_dev, int n1, const void* pc2_dev, int n2, int is_f64, double r,
+                             int64_t* pairs_dev, int64_t capacity, void* ws_dev, size_t ws_bytes, void* stream);
+size_t f2p_positives_workspace_bytes(int n1);
+
 /* ---- host-buffer convenience (what a non-torch caller binds; copies are inside the call) ------------- */
 
 /* Single pair, HOST pointers in and out; synchronous.  out_host: naive [2,n2]; spatial: 2*5*n2 slots, the first

@@ -212,3 +212,18 @@ def inlier_ratio(pred_corr, CAD, PC_aligned, threshold):
     if n < 0:
         raise IndexError("correspondence index out of range")
     return np.float32(n) / np.float32(M), int(n)
+
+
+def find_positives(pc1, pc2, r=0.2, chunk=512):
+    """find_positives (dataset/object.py:281-288) restated in NumPy in row chunks (same ufuncs, same dtype rules, same
+    np.argwhere order; the reference materialises the whole [n1,n2,3] difference tensor)."""
+    pc1 = np.asarray(pc1); pc2 = np.asarray(pc2)
+    out = []
+    for lo in range(0, pc1.shape[0], chunk):
+        d = pc1[lo:lo + chunk, np.newaxis] - pc2
+        s = d * d                                            # np.linalg.norm: sqrt(add.reduce((x.conj()*x).real, axis))
+        dist = np.sqrt(np.add.reduce(s, axis=2))
+        hit = np.argwhere(dist <= r)
+        hit[:, 0] += lo
+        out.append(hit)
+    return np.concatenate(out, 0) if out else np.zeros((0, 2), np.int64)

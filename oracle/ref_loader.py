@@ -77,3 +77,24 @@ def load_reference_utils():
         if saved_gin is None:
             del sys.modules["gin"]
     return mod
+
+
+def load_reference_method(rel_path, class_name, func_name):
+    """Compiles ONE method of a reference class from its unmodified source text, without importing the module (whose
+    top-level imports — open3d, robust_laplacian ... — are not installed here).  Used for `base_object_dataset.find_positives`
+    (dataset/object.py:281-288), which only needs NumPy."""
+    import ast
+    import numpy as np
+    path = os.path.join(REFERENCE_ROOT, rel_path)
+    src = open(path).read()
+    tree = ast.parse(src)
+    for node in ast.walk(tree):
+        if isinstance(node, ast.ClassDef) and node.name == class_name:
+            for item in node.body:
+                if isinstance(item, ast.FunctionDef) and item.name == func_name:
+                    code = ast.get_source_segment(src, item)
+                    import textwrap
+                    ns = {"np": np}
+                    exec(compile(textwrap.dedent(code), path, "exec"), ns)
+                    return ns[func_name]
+    raise RuntimeError(f"{class_name}.{func_name} not found in {path}")

@@ -426,3 +426,39 @@ def test_inlier_ratio_batched_on_solver_output(solvers, oracle):
     with pytest.raises(IndexError):
         from fmap2pointmap_solvers import compute_inlier_ratio
         compute_inlier_ratio(torch.tensor([[0, 5000]]).cuda(), cad[0], aligned[0].cuda(), 1.0)
+
+
+# ---------------------------------------------------------------------------------------------- find_positives
+from golden.positives_cases import POS_CASES  # noqa: E402
+
+
+@pytest.mark.parametrize("name", list(POS_CASES))
+def test_find_positives_matches_reference_golden(solvers, oracle, name):
+    """find_positives / get_overlap drop-ins (dataset/object.py:281-288, :311-317) vs the reference's own output."""
+    import os
+    from fmap2pointmap_solvers.positives import find_positives, find_positives_with_overlap, get_overlap
+    from golden.positives_cases import build_positives_inputs
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "positives_golden.npz"))
+    a, b, r = build_positives_inputs(name)
+    if float(g[name + "/in_sum"]) != float(a.astype(np.float64).sum() + b.astype(np.float64).sum()):
+        pytest.skip("NumPy RNG stream changed")
+    want = g[name + "/P"]
+    got = find_positives(a, b, r=r)
+    assert isinstance(got, np.ndarray) and got.dtype == np.int64
+    np.testing.assert_array_equal(got, want)
+    P, o12, o21 = find_positives_with_overlap(torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda(), r)
+    assert P.is_cuda and o12.dtype == torch.int8
+    np.testing.assert_array_equal(P.cpu().numpy(), want)
+    w12, w21 = get_overlap(a.shape[0], b.shape[0], want)
+    np.testing.assert_array_equal(o12.cpu().numpy(), w12)
+    np.testing.assert_array_equal(o21.cpu().numpy(), w21)
+
+
+def test_find_positives_edge_shapes(solvers, oracle):
+    from fmap2pointmap_solvers.positives import find_positives
+    rng = np.random.default_rng(0)
+    for n1, n2 in [(0, 5), (5, 0), (1, 1), (33, 31), (257, 1000)]:
+        a, b = rng.random((n1, 3)), rng.random((n2, 3))
+        got = find_positives(a, b, r=0.4)
+        want = oracle.find_positives(a, b, 0.4) if n1 and n2 else np.zeros((0, 2), np.int64)
+        np.testing.assert_array_equal(got, want)

@@ -1,5 +1,7 @@
 """CPU tests: the oracle (oracle/f2p_oracle.c and oracle/aten_port.py) against the golden vectors made from the
 unmodified reference, and against the live reference when /root/reference exists (build container only)."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -144,3 +146,37 @@ def test_oracle_inlier_ratio_matches_live_reference():
         got, _ = O.inlier_ratio(corr.numpy(), CAD, PCa, float(thr))
         assert np.float32(float(want)).view(np.int32) == np.float32(got).view(np.int32)
     assert ru.compute_inlier_ratio(corr[:0], CAD, PCa, 1.0) == 0 and O.inlier_ratio(corr[:0].numpy(), CAD, PCa, 1.0)[0] == 0
+
+
+# ---------------------------------------------------------------------------------------------- find_positives
+def _pos_case(name):
+    from golden.positives_cases import build_positives_inputs
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "positives_golden.npz"))
+    a, b, r = build_positives_inputs(name)
+    if float(g[name + "/in_sum"]) != float(a.astype(np.float64).sum() + b.astype(np.float64).sum()):
+        pytest.skip("NumPy RNG stream changed: inputs differ from the ones the golden output was made from")
+    return a, b, r, g[name + "/P"]
+
+
+from golden.positives_cases import POS_CASES  # noqa: E402
+
+
+@pytest.mark.parametrize("name", list(POS_CASES))
+def test_oracle_find_positives_matches_reference_golden(name):
+    a, b, r, want = _pos_case(name)
+    got = O.find_positives(a, b, r, chunk=193)
+    assert got.dtype == np.int64
+    np.testing.assert_array_equal(got, want)
+
+
+@pytest.mark.skipif(not reference_available(), reason="/root/reference only exists in the build container")
+def test_oracle_find_positives_matches_live_reference():
+    from oracle.ref_loader import load_reference_method
+    fp = load_reference_method("dataset/object.py", "base_object_dataset", "find_positives")
+    rng = np.random.default_rng(9)
+    a = rng.random((900, 3)) * 10
+    b = a[rng.integers(0, 900, 600)] + rng.normal(0, 0.5, (600, 3))
+    for r in (0.3, 0.8625):
+        np.testing.assert_array_equal(O.find_positives(a, b, r), fp(None, a, b, r=r))
+        np.testing.assert_array_equal(O.find_positives(a.astype(np.float32), b.astype(np.float32), r),
+                                      fp(None, a.astype(np.float32), b.astype(np.float32), r=r))
