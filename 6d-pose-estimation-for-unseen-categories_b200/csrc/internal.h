@@ -4,15 +4,28 @@
 
 namespace f2p {
 
-// Row splits per column tile.  Two goals: (1) at least ~2 waves of CTAs (2 CTAs/SM) even for one small pair, with
-// >= 2 row tiles per item; (2) for big problems ~40 waves so the last partial wave costs < 3%, while every item still
-// streams >= 16 row tiles (amortises the resident column-operand load and the final cross-thread reduction).
+// Row splits per column tile.  Big problems: ~40 waves of 2 CTAs/SM so the last partial wave costs < 3 %, while every
+// item still streams >= 16 row tiles (amortises the resident column-operand load and the per-CTA bootstrap).
+// Small problems (a few waves at most, e.g. one 5k x 2k pair = 16 column tiles): the split count is chosen by a wave
+// model — time ~ waves x (fixed per-CTA cost + row tiles per item), fixed ~ 1.5 tile times (descriptor fetch, barrier
+// init, column-operand load, first-tile bootstrap) — so that the grid fills whole waves: 18 splits = 288 CTAs = one
+// wave on 148 SMs instead of 20 splits = 320 CTAs = one wave plus a 24-CTA tail.
 static inline int choose_nsplit(long long base_items, int nrt, int sm) {
     if (base_items <= 0 || nrt <= 1) return 1;
     const long long slots = 2ll * sm;
+    const long long cap1 = nrt / 2 > 0 ? nrt / 2 : 1, cap2 = nrt / 16 > 0 ? nrt / 16 : 1;
+    if (base_items * cap1 <= 4 * slots) {
+        long long best = 1;
+        double best_cost = 1e300;
+        for (long long ns = 1; ns <= cap1; ++ns) {
+            const long long waves = (base_items * ns + slots - 1) / slots;
+            const double cost = (double)waves * (1.5 + (double)((nrt + ns - 1) / ns));
+            if (cost < best_cost - 1e-9) { best_cost = cost; best = ns; }
+        }
+        return (int)best;
+    }
     long long ns1 = (2 * slots + base_items - 1) / base_items;
     long long ns2 = (40 * slots + base_items - 1) / base_items;
-    const long long cap1 = nrt / 2 > 0 ? nrt / 2 : 1, cap2 = nrt / 16 > 0 ? nrt / 16 : 1;
     if (ns1 > cap1) ns1 = cap1;
     if (ns2 > cap2) ns2 = cap2;
     long long ns = ns1 > ns2 ? ns1 : ns2;
