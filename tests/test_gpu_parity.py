@@ -236,8 +236,9 @@ def test_kernel3_vote_scores_bits_and_mask(solvers, oracle, M):
 @pytest.mark.parametrize("scale", [1e-16, 3e-19, 1e-22])
 def test_kernel3_vote_tiny_nonzero_and_zero_distances(solvers, oracle, scale):
     """Squared distances that are exactly zero (shared CAD vertex / scene point) stay on the packed fast path; nonzero
-    ones below 2^-101 (coordinates ~1e-16 apart and smaller, down to subnormal squares) must take the full-range
-    sqrt_rn redo.  Scores are compared bit for bit with the oracle."""
+    ones below 2^-101 (coordinates ~1e-16 apart and smaller, down to subnormal squares) need the full-range sqrt_rn:
+    filter_init flags the chunks holding such coordinates and their tiles run the scalar variant of the row loop.
+    Scores are compared bit for bit with the oracle."""
     from fmap2pointmap_solvers import _lib
     L = _lib.load()
     M = 700
@@ -266,6 +267,74 @@ def test_kernel3_vote_tiny_nonzero_and_zero_distances(solvers, oracle, scale):
     for r in range(3):                        # nothing is pruned, so every round repeats the same scores
         np.testing.assert_array_equal(scores[r].cpu().numpy().view(np.int32), s0.view(np.int32))
     assert int(meta[0]) == M
+
+
+@pytest.mark.parametrize("bad", [1e-12, -3e-30, 1e19])
+def test_kernel3_vote_mixed_fast_and_exact_tiles(solvers, oracle, bad):
+    """One 256-candidate chunk references a vertex with a coordinate outside the packed square root's proven range
+    (tiny but nonzero, or huge): only the tiles touching that chunk take the scalar variant in round 0, every tile does
+    in the later rounds.  Scores of all three rounds and the survivors must match the oracle bit for bit."""
+    from fmap2pointmap_solvers import _lib
+    from fmap2pointmap_solvers.batched import thresholds
+    L = _lib.load()
+    M = 1500
+    g = torch.Generator().manual_seed(4242)
+    ncad, npc = 900, 400
+    CAD = torch.rand(ncad, 3, generator=g) * 2 - 1
+    PC = torch.rand(npc, 3, generator=g) * 2 - 1
+    p0 = torch.randint(1, ncad, (M,), generator=g)
+    p1 = torch.sort(torch.randint(0, npc, (M,), generator=g)).values
+    Rm = torch.linalg.qr(torch.randn(3, 3, generator=g)).Q
+    good = torch.rand(M, generator=g) < 0.5
+    PC[p1[good]] = CAD[p0[good]] @ Rm.t() + 0.01 * torch.randn(int(good.sum()), 3, generator=g)
+    CAD[0] = torch.tensor([0.25, bad, -0.5])                   # vertex 0 is used by chunk 3 only
+    p0[800:830] = 0
+    p = torch.stack([p0, p1], 0).contiguous()
+    diam = 3.0
+    thr = (ctypes.c_float * 4)(*thresholds(diam))
+    out = torch.zeros(2, M, dtype=torch.int64, device="cuda")
+    meta = torch.zeros(2, dtype=torch.int32, device="cuda")
+    scores = torch.full((3, M), float("nan"), device="cuda")
+    ws = _ws(L.f2p_filter_workspace_bytes(M))
+    cd, pd, pp = CAD.cuda(), PC.cuda(), p.cuda()
+    rc = L.f2p_spatial_filter(cd.data_ptr(), ncad, pd.data_ptr(), npc, pp.data_ptr(), M, thr, out.data_ptr(),
+                              meta.data_ptr(), meta.data_ptr() + 4, None, scores.data_ptr(), ws.data_ptr(),
+                              ws.numel(), None)
+    _lib.check(rc, "f2p_spatial_filter")
+    torch.cuda.synchronize()
+    s0 = oracle.vote_scores(CAD[p0], PC[p1])
+    np.testing.assert_array_equal(scores[0].cpu().numpy().view(np.int32), s0.view(np.int32))
+    want = oracle.spatial_filter(CAD, PC, p, diam)
+    m = int(meta[0])
+    assert m == want.shape[1] and int(meta[1]) & 2 == 0
+    np.testing.assert_array_equal(out.flatten()[:2 * m].view(2, m).cpu().numpy(), want)
+
+
+@pytest.mark.parametrize("where", [3, 700, 1499])
+def test_kernel3_out_of_range_candidate_sets_status(solvers, where):
+    """A candidate index outside CAD / PC raises status bit 1 whichever chunk holds it (per-chunk flags folded by the
+    combine kernel; no zero-initialised word is involved, so the order the init CTAs run in cannot lose it)."""
+    from fmap2pointmap_solvers import _lib
+    L = _lib.load()
+    M, ncad, npc = 1500, 300, 400
+    g = torch.Generator().manual_seed(9)
+    CAD, PC = torch.rand(ncad, 3, generator=g), torch.rand(npc, 3, generator=g)
+    p0 = torch.randint(0, ncad, (M,), generator=g)
+    p1 = torch.sort(torch.randint(0, npc, (M,), generator=g)).values
+    p0[where] = ncad + 5
+    p = torch.stack([p0, p1], 0).contiguous().cuda()
+    thr = (ctypes.c_float * 4)(0.3, 0.15, 0.055, 0.065)
+    out = torch.zeros(2, M, dtype=torch.int64, device="cuda")
+    meta = torch.full((2,), 77, dtype=torch.int32, device="cuda")          # stale words must be overwritten
+    ws = _ws(L.f2p_filter_workspace_bytes(M))
+    cd, pd = CAD.cuda(), PC.cuda()
+    for expect in (2, 0):
+        rc = L.f2p_spatial_filter(cd.data_ptr(), ncad, pd.data_ptr(), npc, p.data_ptr(), M, thr, out.data_ptr(),
+                                  meta.data_ptr(), meta.data_ptr() + 4, None, None, ws.data_ptr(), ws.numel(), None)
+        _lib.check(rc, "f2p_spatial_filter")
+        torch.cuda.synchronize()
+        assert int(meta[1]) & 2 == expect
+        p[0, where] = 1                                                        # second pass: all indices valid
 
 
 def _adversarial_pair(n1, n2, k, seed):
