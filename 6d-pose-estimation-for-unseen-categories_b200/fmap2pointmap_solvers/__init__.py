@@ -12,6 +12,7 @@ from .spacial_filtering import spacial_filtering_fmap2pointmap
 from .naive import naive_fmap2pointmap
 from .batched import naive_batched, spatial_batched
 from .inlier import compute_inlier_ratio, inlier_ratio_batched
+from .gt_map import C_from_sparse_P, C_from_sparse_P_batched
 
 
 @_configurable
@@ -21,4 +22,5 @@ def choose_fmap2pointmap_solver(solver):
 
 
 __all__ = ["naive_fmap2pointmap", "spacial_filtering_fmap2pointmap", "choose_fmap2pointmap_solver",
-           "naive_batched", "spatial_batched", "compute_inlier_ratio", "inlier_ratio_batched"]
+           "naive_batched", "spatial_batched", "compute_inlier_ratio", "inlier_ratio_batched",
+           "C_from_sparse_P", "C_from_sparse_P_batched"]

@@ -29,6 +29,16 @@ class F2PPairDesc(ctypes.Structure):
     ]
 
 
+class F2PLstsqDesc(ctypes.Structure):
+    """Mirror of `F2PLstsqDesc` in include/f2p.h."""
+    _fields_ = [
+        ("p_off", ctypes.c_int64), ("npos", ctypes.c_int64), ("evecs1_off", ctypes.c_int64),
+        ("evecs2_off", ctypes.c_int64), ("n1", ctypes.c_int32), ("n2", ctypes.c_int32),
+    ]
+
+
+F2P_LSTSQ_MAX_K = 64
+
 # every symbol include/f2p.h declares: (restype, argtypes)
 _SIGNATURES = {
     "f2p_version": (ctypes.c_int, []),
@@ -65,6 +75,10 @@ _SIGNATURES = {
     "f2p_find_positives_write": (ctypes.c_int, [_c_vp, ctypes.c_int, _c_vp, ctypes.c_int, ctypes.c_int, ctypes.c_double,
                                                 _c_vp, ctypes.c_int64, _c_vp, ctypes.c_size_t, _c_vp]),
     "f2p_positives_workspace_bytes": (ctypes.c_size_t, [ctypes.c_int]),
+    "f2p_c_from_sparse_p_batched": (ctypes.c_int, [_c_vp, _c_vp, ctypes.c_int64, _c_vp, ctypes.c_int64,
+                                                   ctypes.POINTER(F2PLstsqDesc), ctypes.c_int, ctypes.c_int, _c_vp, _c_vp,
+                                                   _c_vp, ctypes.c_size_t, _c_vp]),
+    "f2p_lstsq_workspace_bytes": (ctypes.c_size_t, [ctypes.POINTER(F2PLstsqDesc), ctypes.c_int, ctypes.c_int]),
     "f2p_measure_fp32_peak": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), _c_vp]),
 }
 

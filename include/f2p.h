@@ -145,6 +145,31 @@ int f2p_find_positives_write(const void* pc1_dev, int n1, const void* pc2_dev, i
                              int64_t* pairs_dev, int64_t capacity, void* ws_dev, size_t ws_bytes, void* stream);
 size_t f2p_positives_workspace_bytes(int n1);
 
+/* ---- ground-truth functional map of a sample (utils/utils.py:67-80 C_from_sparse_P; scripts/eval.py:74, train.py:101) ---- */
+
+/* One least-squares problem of a batch: positives P (int64 [npos,2], rows (i in evecs1, j in evecs2)) at
+ * P_dev + p_off, bases at evecs1_dev + evecs1_off ([n1, >=k], row stride ld1) and evecs2_dev + evecs2_off. */
+typedef struct F2PLstsqDesc {
+    int64_t p_off;        /* in int64 elements (2 per positive) */
+    int64_t npos;
+    int64_t evecs1_off, evecs2_off;   /* in floats */
+    int32_t n1, n2;
+} F2PLstsqDesc;
+
+#define F2P_LSTSQ_MAX_K 64
+
+/* C[pair] (fp32 [k,k] at C_dev + pair*k*k) = argmin_X || evecs2[P[:,1]] X - evecs1[P[:,0]] ||_F, the minimum-norm
+ * solution when the system is rank deficient — what torch.linalg.lstsq(...)[0][:k] returns (driver gelsy, rcond =
+ * eps32*max(npos,k)).  Floating-point contract: the Gram matrices A^T A, A^T B are accumulated in FP64 in a fixed order
+ * (deterministic), solved in FP64 (Cholesky; Jacobi eigen-decomposition + pseudo-inverse when a pivot is small) and
+ * rounded to FP32 once — parity with the reference is by tolerance (tests/test_gpu_parity.py states it).
+ * status_dev[pair]: bit0 = rank deficient (minimum-norm branch), bit1 = an index of P out of range (C = NaN).
+ * Negative indices wrap once, as torch indexing does.  k <= F2P_LSTSQ_MAX_K. */
+int f2p_c_from_sparse_p_batched(const int64_t* P_dev, const float* evecs1_dev, int64_t ld1, const float* evecs2_dev,
+                                int64_t ld2, const F2PLstsqDesc* descs_host, int npairs, int k, float* C_dev,
+                                int32_t* status_dev, void* ws_dev, size_t ws_bytes, void* stream);
+size_t f2p_lstsq_workspace_bytes(const F2PLstsqDesc* descs_host, int npairs, int k);
+
 /* ---- host-buffer convenience (what a non-torch caller binds; copies are inside the call) ------------- */
 
 /* Single pair, HOST pointers in and out; synchronous.  out_host: naive [2,n2]; spatial: 2*5*n2 slots, the first

@@ -227,3 +227,18 @@ def find_positives(pc1, pc2, r=0.2, chunk=512):
         hit[:, 0] += lo
         out.append(hit)
     return np.concatenate(out, 0) if out else np.zeros((0, 2), np.int64)
+
+
+def c_from_sparse_p(P, evecs1, evecs2):
+    """C_from_sparse_P (utils/utils.py:67-80) restated: gather, then the least-squares solution of
+    evecs2[P[:,1]] @ C = evecs1[P[:,0]] with torch's rank rule (rcond = eps32 * max(N, k)); minimum-norm when rank
+    deficient.  Solved in FLOAT64 from the float32 inputs: this is the exact answer both the reference's FP32 gelsy and
+    the device's FP64 normal equations approximate, so tests measure each one's distance to it.  Returns float64 [k,k]."""
+    P = np.asarray(P).astype(np.int64)
+    e1 = np.asarray(evecs1, dtype=np.float32); e2 = np.asarray(evecs2, dtype=np.float32)
+    k = e1.shape[1]
+    if P.shape[0] == 0:
+        return np.zeros((k, k), np.float64)
+    A = e2[P[:, 1]].astype(np.float64); B = e1[P[:, 0]].astype(np.float64)
+    rcond = float(np.finfo(np.float32).eps) * max(A.shape[0], k)
+    return np.linalg.lstsq(A, B, rcond=rcond)[0]

@@ -531,3 +531,75 @@ def test_find_positives_edge_shapes(solvers, oracle):
         got = find_positives(a, b, r=0.4)
         want = oracle.find_positives(a, b, 0.4) if n1 and n2 else np.zeros((0, 2), np.int64)
         np.testing.assert_array_equal(got, want)
+
+
+# ---------------------------------------------------------------------------------------------- C_from_sparse_P
+from golden.lstsq_cases import LSQ_CASES  # noqa: E402
+
+# Tolerances (floating-point kernel): relative Frobenius distance.  The device result is the FP64 normal-equation
+# solution rounded once to FP32, so it sits within FP32 rounding of the exact least-squares solution (the FP64 oracle);
+# the reference's FP32 gelsy result is itself ~cond(A) * 2^-24 away from it (<= 6e-6 in the golden cases).
+LSQ_TOL_VS_FP64 = 5e-7
+LSQ_TOL_VS_REFERENCE = 2e-5
+
+
+def _lsq_golden(name):
+    import os
+    from golden.lstsq_cases import build_lstsq_inputs
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "lstsq_golden.npz"))
+    P, e1, e2, k = build_lstsq_inputs(name)
+    if float(g[name + "/in_sum"]) != float(e1.astype(np.float64).sum() + e2.astype(np.float64).sum() + P.sum()):
+        pytest.skip("NumPy RNG stream changed")
+    return P, e1, e2, k, g[name + "/C"].astype(np.float64)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", list(LSQ_CASES))
+def test_c_from_sparse_p_matches_reference_golden(solvers, oracle, name):
+    """C_from_sparse_P drop-in (utils/utils.py:67-80), called as scripts/eval.py:74 calls it: int32 P, column-sliced
+    bases (read in place through their row stride)."""
+    from fmap2pointmap_solvers import C_from_sparse_P
+    P, e1, e2, k, want = _lsq_golden(name)
+    exact = oracle.c_from_sparse_p(P, e1[:, :k], e2[:, :k])
+    t1, t2 = torch.from_numpy(e1).cuda(), torch.from_numpy(e2).cuda()
+    C = C_from_sparse_P(torch.from_numpy(P).type(torch.int).cuda(), t1[:, :k], t2[:, :k])
+    assert C.is_cuda and C.dtype == torch.float32 and tuple(C.shape) == (k, k)
+    got = C.cpu().numpy().astype(np.float64)
+    assert np.linalg.norm(got - exact) / np.linalg.norm(exact) < LSQ_TOL_VS_FP64
+    assert np.linalg.norm(got - want) / np.linalg.norm(want) < LSQ_TOL_VS_REFERENCE
+    # CPU tensors in -> CPU tensor out, same bits (deterministic: fixed-order slab partials)
+    C2 = C_from_sparse_P(torch.from_numpy(P), torch.from_numpy(e1)[:, :k], torch.from_numpy(e2)[:, :k])
+    assert not C2.is_cuda
+    np.testing.assert_array_equal(C2.numpy().view(np.int32), C.cpu().numpy().view(np.int32))
+
+
+@pytest.mark.gpu
+def test_c_from_sparse_p_batched_ragged_status_and_errors(solvers, oracle):
+    from fmap2pointmap_solvers import C_from_sparse_P, C_from_sparse_P_batched
+    names = ["lsq_small_300x200_k30", "lsq_under_n_lt_k", "lsq_lm_5002x1369_k30", "lsq_dup_rows_rank_def"]
+    cases = [_lsq_golden(n) for n in names]
+    Ps = [torch.from_numpy(c[0]).cuda() for c in cases]
+    e1 = [torch.from_numpy(c[1]).cuda()[:, :30] for c in cases]
+    e2 = [torch.from_numpy(c[2]).cuda()[:, :30] for c in cases]
+    C, status = C_from_sparse_P_batched(Ps, e1, e2, return_status=True)
+    assert tuple(C.shape) == (4, 30, 30)
+    assert status.cpu().tolist() == [0, 1, 0, 1]               # bit0: minimum-norm branch (rank deficient)
+    for i, c in enumerate(cases):
+        exact = oracle.c_from_sparse_p(c[0], c[1][:, :30], c[2][:, :30])
+        assert np.linalg.norm(C[i].cpu().numpy() - exact) / np.linalg.norm(exact) < LSQ_TOL_VS_FP64
+        single = C_from_sparse_P(Ps[i], e1[i], e2[i])
+        np.testing.assert_array_equal(single.cpu().numpy().view(np.int32), C[i].cpu().numpy().view(np.int32))
+    # no positives at all: the minimum-norm solution is 0 (torch returns zeros as well)
+    Z = C_from_sparse_P(torch.zeros((0, 2), dtype=torch.int64).cuda(), e1[0], e2[0])
+    assert float(Z.abs().max()) == 0.0
+    # negative indices wrap like torch indexing; out-of-range raises IndexError
+    Pn = Ps[0].clone()
+    Pn[:, 1] -= e2[0].shape[0]
+    np.testing.assert_array_equal(C_from_sparse_P(Pn, e1[0], e2[0]).cpu().numpy().view(np.int32),
+                                  C[0].cpu().numpy().view(np.int32))
+    Pb = Ps[0].clone()
+    Pb[5, 0] = e1[0].shape[0]
+    with pytest.raises(IndexError):
+        C_from_sparse_P(Pb, e1[0], e2[0])
+    with pytest.raises(ValueError):
+        C_from_sparse_P(Ps[0], torch.zeros(300, 65).cuda(), torch.zeros(200, 65).cuda())      # k > 64

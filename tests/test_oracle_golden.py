@@ -180,3 +180,45 @@ def test_oracle_find_positives_matches_live_reference():
         np.testing.assert_array_equal(O.find_positives(a, b, r), fp(None, a, b, r=r))
         np.testing.assert_array_equal(O.find_positives(a.astype(np.float32), b.astype(np.float32), r),
                                       fp(None, a.astype(np.float32), b.astype(np.float32), r=r))
+
+
+# ---------------------------------------------------------------------------------------------- C_from_sparse_P
+from golden.lstsq_cases import LSQ_CASES  # noqa: E402
+
+LSQ_REF_TOL = 2e-5     # relative Frobenius distance of the reference's FP32 gelsy result to the FP64 solution
+
+
+def _lsq_case(name):
+    from golden.lstsq_cases import build_lstsq_inputs
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "lstsq_golden.npz"))
+    P, e1, e2, k = build_lstsq_inputs(name)
+    if float(g[name + "/in_sum"]) != float(e1.astype(np.float64).sum() + e2.astype(np.float64).sum() + P.sum()):
+        pytest.skip("NumPy RNG stream changed: inputs differ from the ones the golden output was made from")
+    return P, e1, e2, k, g[name + "/C"]
+
+
+@pytest.mark.parametrize("name", list(LSQ_CASES))
+def test_oracle_c_from_sparse_p_matches_reference_golden(name):
+    """The FP64 restatement (same rank rule) and the reference's FP32 result agree to the reference's own rounding
+    error, in full-rank, square, underdetermined and rank-deficient cases alike."""
+    P, e1, e2, k, want = _lsq_case(name)
+    got = O.c_from_sparse_p(P, e1[:, :k], e2[:, :k])
+    assert got.shape == (k, k)
+    rel = np.linalg.norm(got - want.astype(np.float64)) / np.linalg.norm(got)
+    assert rel < LSQ_REF_TOL, rel
+
+
+@pytest.mark.skipif(not reference_available(), reason="/root/reference only exists in the build container")
+def test_oracle_c_from_sparse_p_matches_live_reference():
+    import torch
+    from oracle.ref_loader import load_reference_utils
+    ru = load_reference_utils()
+    rng = np.random.default_rng(21)
+    e1 = rng.normal(0, 1, (400, 40)).astype(np.float32)
+    e2 = rng.normal(0, 1, (300, 40)).astype(np.float32)
+    for npos in (500, 30, 7):
+        P = np.stack([rng.integers(0, 400, npos), rng.integers(0, 300, npos)], 1)
+        want = ru.C_from_sparse_P(torch.from_numpy(P).type(torch.int), torch.from_numpy(e1)[:, :30],
+                                  torch.from_numpy(e2)[:, :30]).numpy().astype(np.float64)
+        got = O.c_from_sparse_p(P, e1[:, :30], e2[:, :30])
+        assert np.linalg.norm(got - want) / np.linalg.norm(got) < LSQ_REF_TOL
