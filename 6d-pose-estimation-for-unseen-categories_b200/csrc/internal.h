@@ -65,4 +65,7 @@ int run_filter_single(const float* cad, int ncad, const float* pc, int npc, cons
 // peak.cu
 int measure_fp32_peak(double* packed, double* scalar, cudaStream_t st);
 
+// positives.cu: exclusive scan of per-row counts (single CTA) -> row offsets + total
+int launch_rowscan(const int* rowcnt, int n, int64_t* rowoff, int64_t* total, cudaStream_t stream);
+
 }  // namespace f2p

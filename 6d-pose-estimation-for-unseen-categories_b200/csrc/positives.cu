@@ -88,6 +88,12 @@ positives_scan_kernel(const int* __restrict__ rowcnt, int n1, int64_t* __restric
     if (tid == 0) *total = s_run;
 }
 
+int launch_rowscan(const int* rowcnt, int n, int64_t* rowoff, int64_t* total, cudaStream_t st) {
+    positives_scan_kernel<<<1, 1024, 0, st>>>(rowcnt, n, rowoff, total);
+    F2P_CUDA(cudaGetLastError());
+    return 0;
+}
+
 template <typename T>
 static int run_count(const void* pc1, int n1, const void* pc2, int n2, double r, int64_t* total, int8_t* ov12, int8_t* ov21,
                      unsigned char* ws, cudaStream_t st) {

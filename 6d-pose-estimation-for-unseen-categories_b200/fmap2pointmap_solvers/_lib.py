@@ -79,6 +79,12 @@ _SIGNATURES = {
                                                    ctypes.POINTER(F2PLstsqDesc), ctypes.c_int, ctypes.c_int, _c_vp, _c_vp,
                                                    _c_vp, ctypes.c_size_t, _c_vp]),
     "f2p_lstsq_workspace_bytes": (ctypes.c_size_t, [ctypes.POINTER(F2PLstsqDesc), ctypes.c_int, ctypes.c_int]),
+    "f2p_tim_graph_count": (ctypes.c_int, [_c_vp, _c_vp, ctypes.c_int, ctypes.c_double, _c_vp, _c_vp, _c_vp, _c_vp,
+                                           ctypes.c_size_t, _c_vp]),
+    "f2p_tim_graph_write": (ctypes.c_int, [_c_vp, _c_vp, ctypes.c_int, ctypes.c_double, _c_vp, ctypes.c_int64, _c_vp,
+                                           ctypes.c_size_t, _c_vp]),
+    "f2p_tim_workspace_bytes": (ctypes.c_size_t, [ctypes.c_int]),
+    "f2p_compute_tims": (ctypes.c_int, [_c_vp, ctypes.c_int, _c_vp, _c_vp, _c_vp]),
     "f2p_measure_fp32_peak": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), _c_vp]),
 }
 

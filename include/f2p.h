@@ -170,6 +170,26 @@ int f2p_c_from_sparse_p_batched(const int64_t* P_dev, const float* evecs1_dev, i
                                 int32_t* status_dev, void* ws_dev, size_t ws_bytes, void* stream);
 size_t f2p_lstsq_workspace_bytes(const F2PLstsqDesc* descs_host, int npairs, int k);
 
+/* ---- pairwise-consistency front half of the TEASER++ solve (TEASER-plusplus/teaser/src/registration.cc) ----
+ * For the configuration scripts/test_teaser.py:363-370 uses (estimate_scaling = false).  src / dst are the N matched
+ * points as float64 [N,3] (the memory layout of TEASER's column-major Eigen 3xN matrices).
+ * PARITY UNPINNED: the reference needs Eigen, which is not in the build image (see csrc/tims.cu). */
+
+/* computeTIMs (registration.cc:481-519) fused with ScaleInliersSelector::solveForScale (:427-445) and the inlier-graph
+ * edge loop (:582-590): pair (i,j), i < j, is an edge iff | |src_j-src_i| - |dst_j-dst_i| | <= beta
+ * (beta = 2*noise_bound*sqrt(cbar2)).  Pass 1 `_count`: *total_dev = E (int64); degree_dev (optional int32 [N]) =
+ * vertex degrees; mask_dev (optional uint8 [N(N-1)/2]) = scale_inliers_mask_ in TIM order.  Pass 2 `_write` (same
+ * arguments and workspace): edges_dev int32 [E,2] = (i,j) in the reference's addEdge order (i ascending, then j). */
+int f2p_tim_graph_count(const double* src_dev, const double* dst_dev, int n, double beta, int64_t* total_dev,
+                        int32_t* degree_dev, uint8_t* mask_dev, void* ws_dev, size_t ws_bytes, void* stream);
+int f2p_tim_graph_write(const double* src_dev, const double* dst_dev, int n, double beta, int32_t* edges_dev,
+                        int64_t capacity, void* ws_dev, size_t ws_bytes, void* stream);
+size_t f2p_tim_workspace_bytes(int n);
+
+/* computeTIMs alone (registration.cc:481-519): vtilde_dev float64 [N(N-1)/2, 3] (= column-major 3 x T),
+ * map_dev (optional) int32 [N(N-1)/2, 2] = (i, j). */
+int f2p_compute_tims(const double* v_dev, int n, double* vtilde_dev, int32_t* map_dev, void* stream);
+
 /* ---- host-buffer convenience (what a non-torch caller binds; copies are inside the call) ------------- */
 
 /* Single pair, HOST pointers in and out; synchronous.  out_host: naive [2,n2]; spatial: 2*5*n2 slots, the first

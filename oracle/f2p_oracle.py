@@ -242,3 +242,28 @@ def c_from_sparse_p(P, evecs1, evecs2):
     A = e2[P[:, 1]].astype(np.float64); B = e1[P[:, 0]].astype(np.float64)
     rcond = float(np.finfo(np.float32).eps) * max(A.shape[0], k)
     return np.linalg.lstsq(A, B, rcond=rcond)[0]
+
+
+# ---- TEASER++ front half (PARITY UNPINNED: Eigen is not in the image, the reference cannot be compiled here) ------
+def compute_tims(v):
+    """computeTIMs (TEASER-plusplus/teaser/src/registration.cc:481-519): v [3,N] float64 ->
+    (vtilde [3, N(N-1)/2], map [2, N(N-1)/2]); segment i holds v_j - v_i for j = i+1..N-1."""
+    v = np.asarray(v, np.float64)
+    n = v.shape[1]
+    iu, ju = np.triu_indices(n, 1)                       # row-major upper triangle = the reference's segment order
+    return v[:, ju] - v[:, iu], np.stack([iu, ju]).astype(np.int32)
+
+
+def scale_inlier_graph(src, dst, noise_bound, cbar2=1.0):
+    """ScaleInliersSelector::solveForScale (registration.cc:427-445) on the TIMs of src / dst and the edge loop of
+    :582-590.  Norms are sqrt((t0^2 + t1^2) + t2^2) — Eigen's packet order for a 3-element column sum (see
+    csrc/tims.cu for why this is an assumption).  Returns (edges int32 [E,2], degree int32 [N], mask bool [T])."""
+    ts, mp = compute_tims(src)
+    td, _ = compute_tims(dst)
+    n1 = np.sqrt((ts[0] * ts[0] + ts[1] * ts[1]) + ts[2] * ts[2])
+    n2 = np.sqrt((td[0] * td[0] + td[1] * td[1]) + td[2] * td[2])
+    beta = 2.0 * float(noise_bound) * np.sqrt(float(cbar2))
+    mask = np.abs(n1 - n2) <= beta
+    edges = mp[:, mask].T.astype(np.int32)
+    degree = np.bincount(edges.ravel(), minlength=np.asarray(src).shape[1]).astype(np.int32)
+    return edges, degree, mask

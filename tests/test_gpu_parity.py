@@ -603,3 +603,33 @@ def test_c_from_sparse_p_batched_ragged_status_and_errors(solvers, oracle):
         C_from_sparse_P(Pb, e1[0], e2[0])
     with pytest.raises(ValueError):
         C_from_sparse_P(Ps[0], torch.zeros(300, 65).cuda(), torch.zeros(200, 65).cuda())      # k > 64
+
+
+# ---------------------------------------------------------------------------------------------- TEASER++ front half
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [0, 1, 2, 33, 257, 1500])
+def test_teaser_front_tims_and_scale_inlier_graph(solvers, oracle, n):
+    """computeTIMs and the scale-consistency inlier graph (registration.cc:481-519, :427-445, :582-590) against the
+    NumPy restatement, bit for bit (FP64 differences, boolean mask, ordered edge list).  The restatement is not pinned
+    to the compiled reference (no Eigen in the image)."""
+    from fmap2pointmap_solvers.teaser_front import compute_tims, scale_inlier_graph
+    rng = np.random.default_rng(100 + n)
+    src = rng.random((3, n)) * 0.3
+    Rm = np.linalg.qr(rng.normal(size=(3, 3)))[0]
+    dst = Rm @ src + rng.normal(0, 0.004, (3, n)) + np.array([[0.1], [-0.2], [0.7]])
+    out = rng.random(n) < 0.4                                   # 40 % outlier correspondences
+    dst[:, out] = rng.random((3, int(out.sum()))) * 0.3
+    vt, mp = compute_tims(src)
+    wvt, wmp = oracle.compute_tims(src)
+    assert vt.shape == (3, n * (n - 1) // 2) and mp.dtype == np.int32
+    np.testing.assert_array_equal(vt.view(np.int64), wvt.view(np.int64))
+    np.testing.assert_array_equal(mp, wmp)
+    edges, degree, mask = scale_inlier_graph(src, dst, noise_bound=0.01, return_mask=True)
+    we, wd, wm = oracle.scale_inlier_graph(src, dst, 0.01)
+    np.testing.assert_array_equal(mask, wm)
+    np.testing.assert_array_equal(edges, we)
+    np.testing.assert_array_equal(degree, wd)
+    if n == 257:                                                # tensors in -> tensors out, on the inputs' device
+        e2, d2 = scale_inlier_graph(torch.from_numpy(src).cuda(), torch.from_numpy(dst).cuda(), 0.01)
+        assert e2.is_cuda and e2.dtype == torch.int32
+        np.testing.assert_array_equal(e2.cpu().numpy(), we)

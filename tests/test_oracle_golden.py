@@ -222,3 +222,24 @@ def test_oracle_c_from_sparse_p_matches_live_reference():
                                   torch.from_numpy(e2)[:, :30]).numpy().astype(np.float64)
         got = O.c_from_sparse_p(P, e1[:, :30], e2[:, :30])
         assert np.linalg.norm(got - want) / np.linalg.norm(got) < LSQ_REF_TOL
+
+
+# ---------------------------------------------------------------------------------------------- TEASER++ front half
+def test_oracle_tims_follow_the_reference_segment_layout():
+    """UNPINNED restatement (no Eigen here): at least the layout rules the reference states in its own comments hold —
+    segment i starts at i*N - i*(i+1)/2, has N-1-i columns, and column c of it is v[:, i+1+c] - v[:, i] with map (i, j)
+    (TEASER-plusplus/teaser/src/registration.cc:489-516); edges appear in that order and degrees count both ends."""
+    rng = np.random.default_rng(5)
+    N = 23
+    v = rng.normal(size=(3, N))
+    vt, mp = O.compute_tims(v)
+    assert vt.shape == (3, N * (N - 1) // 2)
+    for i in range(N - 1):
+        s = i * N - i * (i + 1) // 2
+        np.testing.assert_array_equal(vt[:, s:s + N - 1 - i], v[:, i + 1:] - v[:, i:i + 1])
+        assert (mp[0, s:s + N - 1 - i] == i).all() and (mp[1, s:s + N - 1 - i] == np.arange(i + 1, N)).all()
+    dst = v + rng.normal(0, 0.05, v.shape)
+    edges, degree, mask = O.scale_inlier_graph(v, dst, 0.05)
+    assert 0 < len(edges) < mask.size and (edges[:, 0] < edges[:, 1]).all()
+    assert (np.diff(edges[:, 0] * N + edges[:, 1]) > 0).all()
+    assert degree.sum() == 2 * len(edges)
