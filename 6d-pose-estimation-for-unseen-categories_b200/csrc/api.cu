@@ -1,6 +1,7 @@
 // api.cu — the extern "C" surface of libf2p_sm100.so (declared in include/f2p.h): argument checks,
 // workspace carving, work decomposition and kernel sequencing.  No torch types, no CPU compute path.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 #include <mutex>
 #include <vector>
@@ -8,6 +9,14 @@
 #include "internal.h"
 
 namespace f2p {
+
+// Row tiles an item of the top-5 kernel streams at least (big batches): its bootstrap costs 12 list cuts, so a CTA
+// should amortise it over more tiles than the arg-min kernel needs (F2P_TOP5_MIN_TILES overrides, tools/).
+static int top5_min_tiles() {
+    static const int v = [] { const char* e = getenv("F2P_TOP5_MIN_TILES"); const int x = e ? atoi(e) : 40; return x > 0 ? x : 40; }();
+    return v;
+}
+
 
 static thread_local char g_err[512] = "";
 void set_error(const char* fmt, ...) {
@@ -95,7 +104,7 @@ static int build_plan(const F2PPairDesc* d, int npairs, int k, int spatial, bool
         p.n1 = d[i].n1; p.n2 = d[i].n2; p.ldx = d[i].ldx; p.ldy = d[i].ldy; p.ncad = d[i].ncad; p.npc = d[i].npc;
         memcpy(p.thr, d[i].thr, sizeof(p.thr));
         p.nrt = (p.n1 + TILE - 1) / TILE; p.nct = (p.n2 + TILE - 1) / TILE;
-        const int ns = choose_nsplit(base_items, p.nrt, sm_count());
+        const int ns = choose_nsplit(base_items, p.nrt, sm_count(), spatial ? top5_min_tiles() : 16);
         p.nsplit = ns;
         if (P.ld1_total + p.nrt * (int64_t)TILE > 0x7fffff00ll || P.ld2_total + p.nct * (int64_t)TILE > 0x7fffff00ll ||
             (int64_t)P.total_items + (int64_t)p.nct * ns > 0x7fffff00ll) {

@@ -10,10 +10,10 @@ namespace f2p {
 // model — time ~ waves x (fixed per-CTA cost + row tiles per item), fixed ~ 1.5 tile times (descriptor fetch, barrier
 // init, column-operand load, first-tile bootstrap) — so that the grid fills whole waves: 18 splits = 288 CTAs = one
 // wave on 148 SMs instead of 20 splits = 320 CTAs = one wave plus a 24-CTA tail.
-static inline int choose_nsplit(long long base_items, int nrt, int sm) {
+static inline int choose_nsplit(long long base_items, int nrt, int sm, int min_tiles = 16) {
     if (base_items <= 0 || nrt <= 1) return 1;
     const long long slots = 2ll * sm;
-    const long long cap1 = nrt / 2 > 0 ? nrt / 2 : 1, cap2 = nrt / 16 > 0 ? nrt / 16 : 1;
+    const long long cap1 = nrt / 2 > 0 ? nrt / 2 : 1, cap2 = nrt / min_tiles > 0 ? nrt / min_tiles : 1;
     if (base_items * cap1 <= 4 * slots) {
         long long best = 1;
         double best_cost = 1e300;

@@ -795,30 +795,54 @@ static size_t gated_smem_bytes(int k, int kc, int nstage) {
            2 * TILE * sizeof(int) + (size_t)GatedCfg<K>::CAP * TILE * 8 + 16;
 }
 
-template <int K>
-static int launch_gated(const float* xT, int64_t ld1_total, const float* yT, int64_t ld2_total, int k, const NNParams& prm,
-                        int total_items, cudaStream_t stream) {
-    const char* ek = getenv("F2P_GATED_KC");
-    const int kcv = ek ? atoi(ek) : KC;
+// k-rows per TMA stage of the gated kernels: 15, 16 or 17, whichever pads k least (then fewest stages), so that every
+// stage is full and runs the unrolled loop — k = 50 -> 3 x 17 instead of 3 x 16 + a 2-step tail stage that costs a
+// whole barrier round trip and a rolled loop; k = 30 -> 2 x 15; k = 64 / 128 -> 16.  The padded k-rows are TMA
+// zero-fill on both operands (fma(0, 0, acc) == acc: acc is never -0).  F2P_GATED_KC overrides (tools/nn_time.py).
+static int choose_gated_kc(int k) {
+    static const int forced = [] { const char* e = getenv("F2P_GATED_KC"); return e ? atoi(e) : 0; }();
+    if (forced == 15 || forced == 16 || forced == 17) return forced;
+    int best = 16, best_pad = 1 << 30, best_n = 1 << 30;
+    const int cand[3] = {16, 17, 15};
+    for (int c = 0; c < 3; ++c) {
+        const int n = (k + cand[c] - 1) / cand[c], pad = n * cand[c] - k;
+        if (pad < best_pad || (pad == best_pad && n < best_n)) { best = cand[c]; best_pad = pad; best_n = n; }
+    }
+    return best;
+}
+
+template <int K, int KCV>
+static int launch_gated_kc(const float* xT, int64_t ld1_total, const float* yT, int64_t ld2_total, int k, const NNParams& prm,
+                           int total_items, cudaStream_t stream) {
     CUtensorMap mapX, mapY;
-    int rc = make_tensor_map_2d(&mapX, xT, (uint64_t)ld1_total, (uint64_t)k, (uint64_t)ld1_total, TILE, KC);
+    int rc = make_tensor_map_2d(&mapX, xT, (uint64_t)ld1_total, (uint64_t)k, (uint64_t)ld1_total, TILE, KCV);
     if (rc) return rc;
-    rc = make_tensor_map_2d(&mapY, yT, (uint64_t)ld2_total, (uint64_t)k, (uint64_t)ld2_total, TILE, KC);
+    rc = make_tensor_map_2d(&mapY, yT, (uint64_t)ld2_total, (uint64_t)k, (uint64_t)ld2_total, TILE, KCV);
     if (rc) return rc;
     // Row-norm L1 prefetch: +2 % for the arg-min kernel at 100k x 100k x 128, slightly negative for top-5 (registers).
     // F2P_GATED_NXP overrides (tools/nn_time.py).
     const char* ep = getenv("F2P_GATED_NXP");
     const int nxp = ep ? atoi(ep) : (K == 1 ? 1 : 0);
-    const size_t smem = gated_smem_bytes<K>(k, KC, NSTAGE);
+    const size_t smem = gated_smem_bytes<K>(k, KCV, NSTAGE);
     if (nxp) {
-        F2P_CUDA(cudaFuncSetAttribute(nn_gated_kernel<K, KC, NSTAGE, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        nn_gated_kernel<K, KC, NSTAGE, 1><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);
+        F2P_CUDA(cudaFuncSetAttribute(nn_gated_kernel<K, KCV, NSTAGE, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        nn_gated_kernel<K, KCV, NSTAGE, 1><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);
     } else {
-        F2P_CUDA(cudaFuncSetAttribute(nn_gated_kernel<K, KC, NSTAGE, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        nn_gated_kernel<K, KC, NSTAGE, 0><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);
+        F2P_CUDA(cudaFuncSetAttribute(nn_gated_kernel<K, KCV, NSTAGE, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        nn_gated_kernel<K, KCV, NSTAGE, 0><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);
     }
     F2P_CUDA(cudaGetLastError());
     return 0;
+}
+
+template <int K>
+static int launch_gated(const float* xT, int64_t ld1_total, const float* yT, int64_t ld2_total, int k, const NNParams& prm,
+                        int total_items, cudaStream_t stream) {
+    switch (choose_gated_kc(k)) {
+        case 15: return launch_gated_kc<K, 15>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
+        case 17: return launch_gated_kc<K, 17>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
+        default: return launch_gated_kc<K, 16>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
+    }
 }
 
 size_t argmin_ws_bytes(int64_t ld2_total, int k, int npairs) {
