@@ -364,10 +364,16 @@ __device__ __forceinline__ void gated_compact(int col, float* s_val, uint32_t* s
     int n = s_cnt[col];
     if (n == kept) return;                 // nothing appended since the last cut
     if (n > CAP) n = CAP;                  // overflow: already flagged by the appender
+    // entries [0, kept) are the sorted survivors of the last cut: they seed the list as they are
     u64 key[K]; float raw[K];
 #pragma unroll
-    for (int r = 0; r < K; ++r) { key[r] = ~0ull; raw[r] = __int_as_float(0x7f800000); }
-    for (int e = 0; e < n; ++e) {
+    for (int r = 0; r < K; ++r) {
+        const bool have = r < kept;
+        const float rv = have ? s_val[r * TILE + col] : __int_as_float(0x7f800000);
+        raw[r] = rv;
+        key[r] = have ? make_key(__fsqrt_rn(rv), s_row[r * TILE + col]) : ~0ull;
+    }
+    for (int e = kept; e < n; ++e) {
         float rv = s_val[e * TILE + col];
         u64 kk = make_key(__fsqrt_rn(rv), s_row[e * TILE + col]);
 #pragma unroll
