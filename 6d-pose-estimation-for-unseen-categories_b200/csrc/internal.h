@@ -14,22 +14,26 @@ static inline int choose_nsplit(long long base_items, int nrt, int sm, int min_t
     if (base_items <= 0 || nrt <= 1) return 1;
     const long long slots = 2ll * sm;
     const long long cap1 = nrt / 2 > 0 ? nrt / 2 : 1, cap2 = nrt / min_tiles > 0 ? nrt / min_tiles : 1;
-    if (base_items * cap1 <= 4 * slots) {
-        long long best = 1;
-        double best_cost = 1e300;
-        for (long long ns = 1; ns <= cap1; ++ns) {
-            const long long waves = (base_items * ns + slots - 1) / slots;
-            const double cost = (double)waves * (1.5 + (double)((nrt + ns - 1) / ns));
-            if (cost < best_cost - 1e-9) { best_cost = cost; best = ns; }
-        }
-        return (int)best;
-    }
     long long ns1 = (2 * slots + base_items - 1) / base_items;
     long long ns2 = (40 * slots + base_items - 1) / base_items;
     if (ns1 > cap1) ns1 = cap1;
     if (ns2 > cap2) ns2 = cap2;
-    long long ns = ns1 > ns2 ? ns1 : ns2;
-    return (int)(ns < 1 ? 1 : ns);
+    long long ns_big = ns1 > ns2 ? ns1 : ns2;
+    if (ns_big < 1) ns_big = 1;
+    // few waves (small problems, or mid-size batches whose items may not be split further): whole-wave cost model;
+    // the top-5 kernel (min_tiles > 16) pays ~4 tile times per item for its bootstrap cuts, the arg-min kernel ~1.5
+    if (base_items * cap1 <= 4 * slots || base_items * ns_big <= 8 * slots) {
+        const double fixed = min_tiles > 16 ? 4.0 : 1.5;
+        long long best = 1;
+        double best_cost = 1e300;
+        for (long long ns = 1; ns <= cap1; ++ns) {
+            const long long waves = (base_items * ns + slots - 1) / slots;
+            const double cost = (double)waves * (fixed + (double)((nrt + ns - 1) / ns));
+            if (cost < best_cost - 1e-9) { best_cost = cost; best = ns; }
+        }
+        return (int)best;
+    }
+    return (int)ns_big;
 }
 
 // prep.cu

@@ -1,0 +1,149 @@
+"""Host-resident batches through the solvers with the copies hidden behind the kernels.
+
+`scripts/eval.py:62-87` receives every batch from the DataLoader in host memory and moves it to the device before the
+solver loop.  For a uniform batch given as STACKED host tensors these entry points cut the batch into pair groups and
+run three stream-ordered stages per group — H2D of the group's operands (copy stream), the solver kernels (the
+caller's current stream), D2H of the group's result slots (a second copy stream) — so that group g+1 is uploaded and
+group g-1 downloaded while group g computes.  Pairs are independent (no exchange between groups), so the result is
+bit-identical to the one-shot call.  Inputs should be pinned (`tensor.pin_memory()`): pageable memory still works, but
+the copies then serialise with the host.
+
+    flat, counts, status = spatial_host_pipelined(C, evecs_x, evecs_y, CAD, PC, diam)    # host tensors in and out
+    maps                 = naive_host_pipelined(C, evecs_x, evecs_y)                     # int64 [P,2,V2] on the host
+
+The returned host tensors are pinned buffers cached per shape: consume (or clone) them before the next call of the
+same shape.  All arithmetic runs in the CUDA library; there is no CPU path.
+"""
+import torch
+
+from . import _lib
+from .batched import naive_batched, spatial_batched
+
+_streams = {}
+_host_out = {}
+
+
+def _copy_streams(device):
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    if key not in _streams:
+        _streams[key] = (torch.cuda.Stream(device), torch.cuda.Stream(device))
+    return _streams[key]
+
+
+def _pinned(tag, shape, dtype):
+    key = (tag, tuple(shape), dtype)
+    buf = _host_out.get(key)
+    if buf is None:
+        buf = torch.empty(shape, dtype=dtype, pin_memory=True)
+        _host_out[key] = buf
+    return buf
+
+
+def _groups(n, chunks):
+    chunks = max(1, min(int(chunks), n))
+    step = (n + chunks - 1) // chunks
+    return [(lo, min(n, lo + step)) for lo in range(0, n, step)]
+
+
+def _check_host(*ts):
+    for t in ts:
+        if not isinstance(t, torch.Tensor) or t.is_cuda or t.dim() != 3:
+            raise ValueError("the pipelined entry points take stacked 3-D HOST tensors ([P,n,k] ...)")
+
+
+def _device():
+    if not torch.cuda.is_available():
+        raise RuntimeError("fmap2pointmap_solvers (B200 build) needs a CUDA device: there is no CPU fallback")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def _sl(t, lo, hi):
+    """Group slice of a stacked operand; an operand shared by the whole batch ([1,...]) is passed whole."""
+    return t if t.shape[0] == 1 else t[lo:hi]
+
+
+def _upload(h2d, comp, device, host_ops, lo, hi, dev_ops):
+    with torch.cuda.stream(h2d):
+        for src, dst in zip(host_ops, dev_ops):
+            if src.shape[0] == 1:
+                if lo == 0:
+                    dst.copy_(src, non_blocking=True)
+            else:
+                dst[lo:hi].copy_(src[lo:hi], non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record(h2d)
+    comp.wait_event(ev)
+
+
+def spatial_host_pipelined(C12, evecs_x, evecs_y, CAD, PC, diam_cad, chunks=4, int16_compat=True):
+    """(flat int64 [P, 2*5*V2], counts int32 [P], status int32 [P]) as pinned HOST tensors; pair i's dense [2,M'_i] map
+    is `flat[i, :2*counts[i]].view(2, -1)` (the layout of `spatial_batched(..., packed=True)`)."""
+    _lib.load()
+    _check_host(C12 if C12.dim() == 3 else C12.reshape(-1, C12.shape[-2], C12.shape[-1]), evecs_x, evecs_y, CAD, PC)
+    device = _device()
+    n, n2 = int(evecs_x.shape[0]), int(evecs_y.shape[1])
+    if len(diam_cad) != n:
+        raise ValueError("diam_cad must have one entry per pair")
+    flat_h = _pinned("sp_flat", (n, 10 * n2), torch.int64)
+    meta_h = _pinned("sp_meta", (2, n), torch.int32)
+    if n == 0:
+        return flat_h, meta_h[0], meta_h[1]
+    with torch.cuda.device(device):
+        comp = torch.cuda.current_stream(device)
+        h2d, d2h = _copy_streams(device)
+        h2d.wait_stream(comp)                    # the staging tensors below may reuse memory of work still in flight
+        C3 = C12 if C12.dim() == 3 else C12.reshape(-1, C12.shape[-2], C12.shape[-1])
+        host_ops = [C3.float(), evecs_x.float(), evecs_y.float(), CAD.float(), PC.float()]   # no-ops for float32
+        dev_ops = [torch.empty(t.shape, dtype=torch.float32, device=device) for t in host_ops]
+        for t in dev_ops:
+            t.record_stream(h2d)
+        diam = list(diam_cad)
+        for lo, hi in _groups(n, chunks):
+            _upload(h2d, comp, device, host_ops, lo, hi, dev_ops)
+            flat, counts, status = spatial_batched(*[_sl(t, lo, hi) for t in dev_ops], diam[lo:hi], int16_compat=int16_compat,
+                                                   verbose=False, packed=True)
+            ev = torch.cuda.Event()
+            ev.record(comp)
+            for t in (flat, counts, status):
+                t.record_stream(d2h)
+            with torch.cuda.stream(d2h):
+                d2h.wait_event(ev)
+                flat_h[lo:hi].copy_(flat, non_blocking=True)
+                meta_h[0, lo:hi].copy_(counts, non_blocking=True)
+                meta_h[1, lo:hi].copy_(status, non_blocking=True)
+        d2h.synchronize()
+    if bool((meta_h[1] & 2).any()):
+        bad = int((meta_h[1] & 2).nonzero()[0][0])
+        raise IndexError(f"pair {bad}: candidate index out of range of CAD/PC")
+    return flat_h, meta_h[0], meta_h[1]
+
+
+def naive_host_pipelined(C12, evecs_x, evecs_y, chunks=4, int16_compat=False):
+    """int64 [P,2,V2] index maps as one pinned HOST tensor."""
+    _lib.load()
+    C3 = C12 if C12.dim() == 3 else C12.reshape(-1, C12.shape[-2], C12.shape[-1])
+    _check_host(C3, evecs_x, evecs_y)
+    device = _device()
+    n, n2 = int(evecs_x.shape[0]), int(evecs_y.shape[1])
+    out_h = _pinned("nv", (n, 2, n2), torch.int64)
+    if n == 0 or n2 == 0:
+        return out_h
+    with torch.cuda.device(device):
+        comp = torch.cuda.current_stream(device)
+        h2d, d2h = _copy_streams(device)
+        h2d.wait_stream(comp)
+        host_ops = [C3.float(), evecs_x.float(), evecs_y.float()]
+        dev_ops = [torch.empty(t.shape, dtype=torch.float32, device=device) for t in host_ops]
+        for t in dev_ops:
+            t.record_stream(h2d)
+        for lo, hi in _groups(n, chunks):
+            _upload(h2d, comp, device, host_ops, lo, hi, dev_ops)
+            maps = naive_batched(*[_sl(t, lo, hi) for t in dev_ops], int16_compat=int16_compat)
+            ev = torch.cuda.Event()
+            ev.record(comp)
+            maps.record_stream(d2h)
+            with torch.cuda.stream(d2h):
+                d2h.wait_event(ev)
+                out_h[lo:hi].copy_(maps, non_blocking=True)
+        d2h.synchronize()
+    return out_h

@@ -633,3 +633,36 @@ def test_teaser_front_tims_and_scale_inlier_graph(solvers, oracle, n):
         e2, d2 = scale_inlier_graph(torch.from_numpy(src).cuda(), torch.from_numpy(dst).cuda(), 0.01)
         assert e2.is_cuda and e2.dtype == torch.int32
         np.testing.assert_array_equal(e2.cpu().numpy(), we)
+
+
+# ---------------------------------------------------------------------------------------------- pipelined host batches
+@pytest.mark.gpu
+@pytest.mark.parametrize("chunks", [1, 3, 16])
+def test_host_pipelined_batches_match_one_shot_calls(solvers, oracle, chunks):
+    """Stacked HOST batches cut into pair groups (H2D / kernels / D2H on three streams) give the very same maps as the
+    one-shot device call, for both solvers, with pinned and pageable inputs and a C shared by the batch."""
+    from fmap2pointmap_solvers.batched import naive_batched, spatial_batched
+    from fmap2pointmap_solvers.pipeline import naive_host_pipelined, spatial_host_pipelined
+    g = torch.Generator().manual_seed(31)
+    P, n1, n2, k = 7, 300, 130, 20
+    ex = torch.randn(P, n1, k, generator=g)
+    ey = torch.randn(P, n2, k, generator=g)
+    C = torch.eye(k).repeat(P, 1, 1) + 0.05 * torch.randn(P, k, k, generator=g)
+    cad = torch.rand(P, n1, 3, generator=g)
+    pc = torch.rand(P, n2, 3, generator=g)
+    diam = [1.7 + 0.1 * i for i in range(P)]
+    want = naive_batched(C.cuda(), ex.cuda(), ey.cuda()).cpu()
+    got = naive_host_pipelined(C.pin_memory(), ex.pin_memory(), ey.pin_memory(), chunks=chunks)
+    assert not got.is_cuda and got.is_pinned()
+    assert torch.equal(got, want)
+    for i in (0, P - 1):
+        np.testing.assert_array_equal(got[i].numpy(), oracle.naive(C[i], ex[i], ey[i], int16_compat=False))
+    wflat, wcnt, wst = spatial_batched(C.cuda(), ex.cuda(), ey.cuda(), cad.cuda(), pc.cuda(), diam, verbose=False, packed=True)
+    flat, cnt, st = spatial_host_pipelined(C, ex, ey, cad, pc, diam, chunks=chunks)          # pageable inputs
+    assert torch.equal(cnt, wcnt.cpu()) and torch.equal(st, wst.cpu())
+    for i in range(P):
+        m = int(cnt[i])
+        assert torch.equal(flat[i, :2 * m], wflat[i, :2 * m].cpu())
+    # one C shared by all pairs
+    want1 = naive_batched(C[:1].cuda(), ex.cuda(), ey.cuda()).cpu()
+    assert torch.equal(naive_host_pipelined(C[0], ex, ey, chunks=chunks), want1)
