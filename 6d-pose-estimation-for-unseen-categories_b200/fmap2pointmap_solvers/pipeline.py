@@ -147,3 +147,4 @@ def naive_host_pipelined(C12, evecs_x, evecs_y, chunks=4, int16_compat=False):
                 out_h[lo:hi].copy_(maps, non_blocking=True)
         d2h.synchronize()
     return out_h
+

@@ -666,3 +666,4 @@ def test_host_pipelined_batches_match_one_shot_calls(solvers, oracle, chunks):
     # one C shared by all pairs
     want1 = naive_batched(C[:1].cuda(), ex.cuda(), ey.cuda()).cpu()
     assert torch.equal(naive_host_pipelined(C[0], ex, ey, chunks=chunks), want1)
+
