@@ -1,4 +1,4 @@
-// prep.cu — kernel 1: spectral projection into the k-major operand layout, plus ATen-ordered row norms.
+// prep.cu — kernel 1: spectral projection into the k-major operand layout with fused ATen-ordered row norms.
 //
 // Replaces `torch.matmul(evecs_x, C12.t())` (naive.py:20, spacial_filtering.py:19) and the
 // `x.pow(2).sum(-1)` norms that torch.cdist's matmul path forms (naive.py:33 -> ATen _euclidean_dist).
@@ -14,15 +14,65 @@ namespace f2p {
 constexpr int PREP_THREADS = 256;
 constexpr int EPAD = TILE + 1;  // padded row of the transposed evecs tile: conflict-free transposed stores
 
+// ATen `x.pow(2).sum(-1)` of one point whose k values sit at p[c * stride]: 8 lanes x ILP-4 partial sums (k < 8: four
+// interleaved scalar chains), squares rounded first.  `scale` is an exact power of two (-0.5 recovers feat from -2*feat).
+__device__ __forceinline__ float aten_sqnorm(const float* p, int64_t stride, int k, float scale) {
+    if (k < 8) {
+        // scalar_inner_sum: 4 interleaved chains, leftovers into chain 0
+        float q[4] = {0.f, 0.f, 0.f, 0.f};
+        const int s4 = k / 4;
+        for (int rr = 0; rr < s4; ++rr)
+#pragma unroll
+            for (int l = 0; l < 4; ++l) { const float v = scale * p[(4 * rr + l) * stride]; q[l] = __fadd_rn(q[l], __fmul_rn(v, v)); }
+        for (int t2 = 4 * s4; t2 < k; ++t2) { const float v = scale * p[t2 * stride]; q[0] = __fadd_rn(q[0], __fmul_rn(v, v)); }
+        q[0] = __fadd_rn(q[0], q[1]); q[0] = __fadd_rn(q[0], q[2]); q[0] = __fadd_rn(q[0], q[3]);
+        return q[0];
+    }
+    const int nv = k / 8, g = nv / 4;
+    float P[4][8];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int l = 0; l < 8; ++l) P[j][l] = 0.f;
+    for (int rr = 0; rr < g; ++rr) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int l = 0; l < 8; ++l) {
+                const float v = scale * p[(32 * rr + 8 * j + l) * stride];
+                P[j][l] = __fadd_rn(P[j][l], __fmul_rn(v, v));
+            }
+    }
+    for (int v8 = 4 * g; v8 < nv; ++v8)
+#pragma unroll
+        for (int l = 0; l < 8; ++l) {
+            const float v = scale * p[(8 * v8 + l) * stride];
+            P[0][l] = __fadd_rn(P[0][l], __fmul_rn(v, v));
+        }
+#pragma unroll
+    for (int l = 0; l < 8; ++l) {
+        P[0][l] = __fadd_rn(P[0][l], P[1][l]);
+        P[0][l] = __fadd_rn(P[0][l], P[2][l]);
+        P[0][l] = __fadd_rn(P[0][l], P[3][l]);
+    }
+    float f = 0.f;
+    for (int t2 = 8 * nv; t2 < k; ++t2) { const float v = scale * p[t2 * stride]; f = __fadd_rn(f, __fmul_rn(v, v)); }
+#pragma unroll
+    for (int l = 0; l < 8; ++l) f = __fadd_rn(f, P[0][l]);
+    return f;
+}
+
 // grid.x = total row tiles over all pairs (x operand) or column tiles (y operand).
-// smem: eT[k][EPAD] + Cs[k][8]
+// smem: eT[k][EPAD] + Cs[2][k][8] (+ fT[k][EPAD] when C is given: the projected rows, kept for the fused norms)
 template <bool IS_X>
 __global__ void __launch_bounds__(PREP_THREADS)
 project_kernel(const float* __restrict__ evecs, const float* __restrict__ Cmat, const PairDev* __restrict__ pairs,
-               int npairs, int uniform_tiles, int k, float* __restrict__ outT, int64_t ld_total) {
+               int npairs, int uniform_tiles, int k, float* __restrict__ outT, int64_t ld_total,
+               float* __restrict__ nrm, int use_ft) {
     extern __shared__ float smem[];
     float* eT = smem;                 // [k][EPAD]
     float* Cs = smem + (((size_t)k * EPAD + 3) & ~(size_t)3);  // 2 x [k][8], 16-byte aligned
+    float* fT = Cs + (size_t)k * 16;  // [k][EPAD]
     const int tid = threadIdx.x;
     const int pi = find_pair(blockIdx.x, pairs, npairs, uniform_tiles, IS_X ? &PairDev::xtile0 : &PairDev::ytile0);
     const PairDev pd = pairs[pi];
@@ -47,6 +97,8 @@ project_kernel(const float* __restrict__ evecs, const float* __restrict__ Cmat, 
     if (Cmat == nullptr) {
         // transpose only: outT[c][col0+r] = e[r][c]
         for (int c = half; c < k; c += 2) outT[(int64_t)c * ld_total + col0 + r] = eT[c * EPAD + r];
+        // norms of the rows as they are (padding rows: +inf for the streamed operand so they never win, else 0)
+        if (tid < TILE) nrm[col0 + tid] = (row0 + tid < n) ? aten_sqnorm(eT + tid, EPAD, k, 1.f) : (IS_X ? __int_as_float(0x7f800000) : 0.f);
         return;
     }
     const float* Cp = Cmat + pd.c_off;
@@ -75,82 +127,17 @@ project_kernel(const float* __restrict__ evecs, const float* __restrict__ Cmat, 
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
             const int a = a0 + half * 8 + q;
-            if (a < k) outT[(int64_t)a * ld_total + col0 + r] = -2.0f * acc[q];
+            if (a < k) { outT[(int64_t)a * ld_total + col0 + r] = -2.0f * acc[q]; if (use_ft) fT[a * EPAD + r] = acc[q]; }
         }
     }
-}
-
-// ATen `x.pow(2).sum(-1)` over the k-major operand: thread per point, coalesced reads down the k axis.
-// scale = -0.5 recovers feat_x from xT exactly; scale = 1 for the y operand.
-template <bool IS_X>
-__global__ void __launch_bounds__(256)
-rownorm_kernel(const float* __restrict__ opT, const PairDev* __restrict__ pairs, int npairs, int uniform_tiles,
-               int k, int64_t ld_total, float* __restrict__ nrm) {
-    const int tileid = blockIdx.x >> 0;
-    // each block covers 256 consecutive columns = 2 tiles; decode by the first tile
-    const int t0 = tileid * 2;
-    for (int h = 0; h < 2; ++h) {
-        const int t = t0 + h;
-        const int total = IS_X ? (pairs[npairs - 1].xtile0 + pairs[npairs - 1].nrt) : (pairs[npairs - 1].ytile0 + pairs[npairs - 1].nct);
-        if (t >= total) return;
-        if ((threadIdx.x >> 7) != h) continue;
-        const int pi = find_pair(t, pairs, npairs, uniform_tiles, IS_X ? &PairDev::xtile0 : &PairDev::ytile0);
-        const PairDev& pd = pairs[pi];
-        const int tile = t - (IS_X ? pd.xtile0 : pd.ytile0);
-        const int r = threadIdx.x & 127;
-        const int gi = tile * TILE + r;
-        const int n = IS_X ? pd.n1 : pd.n2;
-        const int64_t col = (int64_t)(IS_X ? pd.x_col0 : pd.y_col0) + gi;
-        const float scale = IS_X ? -0.5f : 1.0f;
-        const float* p = opT + col;
-        float result;
-        if (gi >= n) {
-            result = IS_X ? __int_as_float(0x7f800000) : 0.f;
-        } else if (k < 8) {
-            // scalar_inner_sum: 4 interleaved chains, leftovers into chain 0
-            float q[4] = {0.f, 0.f, 0.f, 0.f};
-            const int s4 = k / 4;
-            for (int rr = 0; rr < s4; ++rr)
-#pragma unroll
-                for (int l = 0; l < 4; ++l) { const float v = scale * p[(int64_t)(4 * rr + l) * ld_total]; q[l] = __fadd_rn(q[l], __fmul_rn(v, v)); }
-            for (int t2 = 4 * s4; t2 < k; ++t2) { const float v = scale * p[(int64_t)t2 * ld_total]; q[0] = __fadd_rn(q[0], __fmul_rn(v, v)); }
-            q[0] = __fadd_rn(q[0], q[1]); q[0] = __fadd_rn(q[0], q[2]); q[0] = __fadd_rn(q[0], q[3]);
-            result = q[0];
-        } else {
-            const int nv = k / 8, g = nv / 4;
-            float P[4][8];
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-#pragma unroll
-                for (int l = 0; l < 8; ++l) P[j][l] = 0.f;
-            for (int rr = 0; rr < g; ++rr) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-#pragma unroll
-                    for (int l = 0; l < 8; ++l) {
-                        const float v = scale * p[(int64_t)(32 * rr + 8 * j + l) * ld_total];
-                        P[j][l] = __fadd_rn(P[j][l], __fmul_rn(v, v));
-                    }
-            }
-            for (int v8 = 4 * g; v8 < nv; ++v8)
-#pragma unroll
-                for (int l = 0; l < 8; ++l) {
-                    const float v = scale * p[(int64_t)(8 * v8 + l) * ld_total];
-                    P[0][l] = __fadd_rn(P[0][l], __fmul_rn(v, v));
-                }
-#pragma unroll
-            for (int l = 0; l < 8; ++l) {
-                P[0][l] = __fadd_rn(P[0][l], P[1][l]);
-                P[0][l] = __fadd_rn(P[0][l], P[2][l]);
-                P[0][l] = __fadd_rn(P[0][l], P[3][l]);
-            }
-            float f = 0.f;
-            for (int t2 = 8 * nv; t2 < k; ++t2) { const float v = scale * p[(int64_t)t2 * ld_total]; f = __fadd_rn(f, __fmul_rn(v, v)); }
-#pragma unroll
-            for (int l = 0; l < 8; ++l) f = __fadd_rn(f, P[0][l]);
-            result = f;
-        }
-        nrm[col] = result;
+    // fused row norms of the projected points: from the shared-memory copy, or (k too large for a second [k][129]
+    // buffer) from this CTA's own stores, which the barrier makes visible
+    __syncthreads();
+    if (tid < TILE) {
+        float v = IS_X ? __int_as_float(0x7f800000) : 0.f;
+        if (row0 + tid < n)
+            v = use_ft ? aten_sqnorm(fT + tid, EPAD, k, 1.f) : aten_sqnorm(outT + col0 + tid, ld_total, k, -0.5f);
+        nrm[col0 + tid] = v;
     }
 }
 
@@ -159,17 +146,17 @@ int launch_project(bool is_x, const float* evecs, const float* Cmat, const PairD
                    int uniform_tiles, int total_tiles, int k, float* outT, int64_t ld_total, float* nrm,
                    cudaStream_t stream) {
     if (total_tiles <= 0) return 0;
-    const size_t smem = ((((size_t)k * EPAD + 3) & ~(size_t)3) + (size_t)k * 16) * sizeof(float);
+    const size_t base = ((((size_t)k * EPAD + 3) & ~(size_t)3) + (size_t)k * 16) * sizeof(float);
+    const int use_ft = Cmat && base + (size_t)k * EPAD * sizeof(float) <= 112 * 1024;   // keep 2 CTAs per SM
+    const size_t smem = base + (use_ft ? (size_t)k * EPAD * sizeof(float) : 0);
     if (is_x) {
         static bool attr_done = false;
-        if (!attr_done) { F2P_CUDA(cudaFuncSetAttribute(project_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); attr_done = true; }
-        project_kernel<true><<<total_tiles, PREP_THREADS, smem, stream>>>(evecs, Cmat, pairs_dev, npairs, uniform_tiles, k, outT, ld_total);
-        rownorm_kernel<true><<<(total_tiles + 1) / 2, 256, 0, stream>>>(outT, pairs_dev, npairs, uniform_tiles, k, ld_total, nrm);
+        if (!attr_done) { F2P_CUDA(cudaFuncSetAttribute(project_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024)); attr_done = true; }
+        project_kernel<true><<<total_tiles, PREP_THREADS, smem, stream>>>(evecs, Cmat, pairs_dev, npairs, uniform_tiles, k, outT, ld_total, nrm, use_ft);
     } else {
         static bool attr_done = false;
-        if (!attr_done) { F2P_CUDA(cudaFuncSetAttribute(project_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); attr_done = true; }
-        project_kernel<false><<<total_tiles, PREP_THREADS, smem, stream>>>(evecs, Cmat, pairs_dev, npairs, uniform_tiles, k, outT, ld_total);
-        rownorm_kernel<false><<<(total_tiles + 1) / 2, 256, 0, stream>>>(outT, pairs_dev, npairs, uniform_tiles, k, ld_total, nrm);
+        if (!attr_done) { F2P_CUDA(cudaFuncSetAttribute(project_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024)); attr_done = true; }
+        project_kernel<false><<<total_tiles, PREP_THREADS, smem, stream>>>(evecs, Cmat, pairs_dev, npairs, uniform_tiles, k, outT, ld_total, nrm, use_ft);
     }
     F2P_CUDA(cudaGetLastError());
     return 0;
