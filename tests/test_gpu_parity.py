@@ -667,3 +667,28 @@ def test_host_pipelined_batches_match_one_shot_calls(solvers, oracle, chunks):
     want1 = naive_batched(C[:1].cuda(), ex.cuda(), ey.cuda()).cpu()
     assert torch.equal(naive_host_pipelined(C[0], ex, ey, chunks=chunks), want1)
 
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("k,npos,kind", [(1, 5, "full"), (7, 3, "under"), (9, 40, "dup"), (33, 500, "full"), (64, 2000, "full"),
+                                         (64, 20, "under"), (31, 31, "square")])
+def test_c_from_sparse_p_shapes_vs_fp64_oracle(solvers, oracle, k, npos, kind):
+    """Solver branches the golden cases do not reach: odd k in the Jacobi pseudo-inverse (padded round-robin ordering),
+    the 64-column Gram kernel, k = 1, exactly square systems.  Reference = the FP64 oracle (same rank rule)."""
+    from fmap2pointmap_solvers import C_from_sparse_P_batched
+    rng = np.random.default_rng(1000 * k + npos)
+    n1, n2 = 150, 120
+    e1 = rng.normal(size=(n1, k)).astype(np.float32)
+    e2 = rng.normal(size=(n2, k)).astype(np.float32)
+    cols = rng.integers(0, 4 if kind == "dup" else n2, npos)
+    if kind == "square":
+        cols = rng.permutation(n2)[:npos]                      # distinct rows: full rank almost surely
+    P = np.stack([rng.integers(0, n1, npos), cols], 1).astype(np.int64)
+    exact = oracle.c_from_sparse_p(P, e1, e2)
+    C, status = C_from_sparse_P_batched([torch.from_numpy(P).cuda()], [torch.from_numpy(e1).cuda()],
+                                        [torch.from_numpy(e2).cuda()], return_status=True)
+    got = C[0].cpu().numpy().astype(np.float64)
+    rank_def = kind in ("under", "dup")
+    assert int(status[0]) == (1 if rank_def else 0)
+    tol = 5e-6 if kind == "square" else LSQ_TOL_VS_FP64        # a square random system can be ill-conditioned
+    assert np.linalg.norm(got - exact) <= tol * max(np.linalg.norm(exact), 1e-30)
