@@ -1,5 +1,6 @@
 // internal.h — launcher prototypes shared between the translation units of libf2p_sm100.so.
 #pragma once
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace f2p {
@@ -12,6 +13,10 @@ namespace f2p {
 // wave on 148 SMs instead of 20 splits = 320 CTAs = one wave plus a 24-CTA tail.
 static inline int choose_nsplit(long long base_items, int nrt, int sm, int min_tiles = 16) {
     if (base_items <= 0 || nrt <= 1) return 1;
+    {   // F2P_NSPLIT: fixed split count for experiments (tools/)
+        static const int forced = [] { const char* e = getenv("F2P_NSPLIT"); return e ? atoi(e) : 0; }();
+        if (forced > 0) return forced < nrt ? forced : nrt;
+    }
     const long long slots = 2ll * sm;
     const long long cap1 = nrt / 2 > 0 ? nrt / 2 : 1, cap2 = nrt / min_tiles > 0 ? nrt / min_tiles : 1;
     long long ns1 = (2 * slots + base_items - 1) / base_items;
