@@ -7,7 +7,8 @@ point map in `scripts/test_teaser.py` (`solver.solve(src, dst)` at :431, configu
 `ScaleInliersSelector::solveForScale` (:427-445) and the inlier-graph edge loop (:582-590) and returns the edge list in
 the reference's `addEdge` order plus the vertex degrees, without materialising the TIMs.  NumPy in -> NumPy out,
 tensors in -> tensors out.  The arithmetic runs in csrc/tims.cu (FP64); there is no CPU path.
-Parity with the reference is UNPINNED (Eigen is not available to compile it; see csrc/tims.cu).
+Parity: the inlier mask is pinned to the reference's own fixed-scale fixture (tests/golden/teaser_golden.npz, from
+TEASER-plusplus/test/teaser/data/registration_test); the 3-term summation order is an assumption (csrc/tims.cu).
 """
 import math
 

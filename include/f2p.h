@@ -173,7 +173,9 @@ size_t f2p_lstsq_workspace_bytes(const F2PLstsqDesc* descs_host, int npairs, int
 /* ---- pairwise-consistency front half of the TEASER++ solve (TEASER-plusplus/teaser/src/registration.cc) ----
  * For the configuration scripts/test_teaser.py:363-370 uses (estimate_scaling = false).  src / dst are the N matched
  * points as float64 [N,3] (the memory layout of TEASER's column-major Eigen 3xN matrices).
- * PARITY UNPINNED: the reference needs Eigen, which is not in the build image (see csrc/tims.cu). */
+ * Parity: the inlier mask is pinned to the reference's own fixture (test/teaser/data/registration_test/
+ * fixed_scale_inliers.csv, tests/golden/teaser_golden.npz); the reference itself cannot be compiled here (Eigen is not in
+ * the image), so the order of the 3-term norm sum stays an assumption that the fixture does not exercise (csrc/tims.cu). */
 
 /* computeTIMs (registration.cc:481-519) fused with ScaleInliersSelector::solveForScale (:427-445) and the inlier-graph
  * edge loop (:582-590): pair (i,j), i < j, is an edge iff | |src_j-src_i| - |dst_j-dst_i| | <= beta

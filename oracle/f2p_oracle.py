@@ -244,7 +244,10 @@ def c_from_sparse_p(P, evecs1, evecs2):
     return np.linalg.lstsq(A, B, rcond=rcond)[0]
 
 
-# ---- TEASER++ front half (PARITY UNPINNED: Eigen is not in the image, the reference cannot be compiled here) ------
+# ---- TEASER++ front half ---------------------------------------------------------------------------------------
+# Pinned at mask level to the reference's own fixture (registration_test/fixed_scale_inliers.csv -> tests/golden/
+# teaser_golden.npz, oracle/make_golden_teaser.py).  The reference cannot be compiled here (no Eigen), so the order of
+# the 3-term norm sum is an assumption; it matters only for a statistic within one ulp of beta, which the fixture has not.
 def compute_tims(v):
     """computeTIMs (TEASER-plusplus/teaser/src/registration.cc:481-519): v [3,N] float64 ->
     (vtilde [3, N(N-1)/2], map [2, N(N-1)/2]); segment i holds v_j - v_i for j = i+1..N-1."""
@@ -254,16 +257,22 @@ def compute_tims(v):
     return v[:, ju] - v[:, iu], np.stack([iu, ju]).astype(np.int32)
 
 
+def scale_inliers(v1, v2, noise_bound, cbar2=1.0):
+    """ScaleInliersSelector::solveForScale (registration.cc:427-445) on two [3,M] measurement matrices: column m is an
+    inlier iff | |v1_m| - |v2_m| | <= beta, beta = 2*noise_bound*sqrt(cbar2).  Norms are sqrt((t0^2 + t1^2) + t2^2) —
+    Eigen's packet order for a 3-element column sum (see csrc/tims.cu for why this is an assumption)."""
+    v1, v2 = np.asarray(v1, np.float64), np.asarray(v2, np.float64)
+    n1 = np.sqrt((v1[0] * v1[0] + v1[1] * v1[1]) + v1[2] * v1[2])
+    n2 = np.sqrt((v2[0] * v2[0] + v2[1] * v2[1]) + v2[2] * v2[2])
+    return np.abs(n1 - n2) <= 2.0 * float(noise_bound) * np.sqrt(float(cbar2))
+
+
 def scale_inlier_graph(src, dst, noise_bound, cbar2=1.0):
-    """ScaleInliersSelector::solveForScale (registration.cc:427-445) on the TIMs of src / dst and the edge loop of
-    :582-590.  Norms are sqrt((t0^2 + t1^2) + t2^2) — Eigen's packet order for a 3-element column sum (see
-    csrc/tims.cu for why this is an assumption).  Returns (edges int32 [E,2], degree int32 [N], mask bool [T])."""
+    """scale_inliers on the TIMs of src / dst and the edge loop of registration.cc:582-590.
+    Returns (edges int32 [E,2], degree int32 [N], mask bool [T])."""
     ts, mp = compute_tims(src)
     td, _ = compute_tims(dst)
-    n1 = np.sqrt((ts[0] * ts[0] + ts[1] * ts[1]) + ts[2] * ts[2])
-    n2 = np.sqrt((td[0] * td[0] + td[1] * td[1]) + td[2] * td[2])
-    beta = 2.0 * float(noise_bound) * np.sqrt(float(cbar2))
-    mask = np.abs(n1 - n2) <= beta
+    mask = scale_inliers(ts, td, noise_bound, cbar2)
     edges = mp[:, mask].T.astype(np.int32)
     degree = np.bincount(edges.ravel(), minlength=np.asarray(src).shape[1]).astype(np.int32)
     return edges, degree, mask

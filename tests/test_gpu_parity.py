@@ -692,3 +692,18 @@ def test_c_from_sparse_p_shapes_vs_fp64_oracle(solvers, oracle, k, npos, kind):
     assert int(status[0]) == (1 if rank_def else 0)
     tol = 5e-6 if kind == "square" else LSQ_TOL_VS_FP64        # a square random system can be ill-conditioned
     assert np.linalg.norm(got - exact) <= tol * max(np.linalg.norm(exact), 1e-30)
+
+
+@pytest.mark.gpu
+def test_teaser_front_matches_the_reference_own_fixture(solvers):
+    """The device kernel against the reference's own fixed-scale inlier fixture (see oracle/make_golden_teaser.py)."""
+    import os
+    from fmap2pointmap_solvers.teaser_front import scale_inlier_graph
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "teaser_golden.npz"))
+    src, dst, full = g["src"], g["dst"], g["inlier_matrix"]
+    n = src.shape[1]
+    iu, ju = np.triu_indices(n, 1)
+    edges, degree, mask = scale_inlier_graph(src, dst, float(g["noise_bound"]), float(g["cbar2"]), return_mask=True)
+    np.testing.assert_array_equal(mask, full[iu, ju])
+    np.testing.assert_array_equal(edges, np.stack([iu, ju], 1)[full[iu, ju]].astype(np.int32))
+    np.testing.assert_array_equal(degree, full.sum(1).astype(np.int32))

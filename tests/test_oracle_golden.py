@@ -226,7 +226,7 @@ def test_oracle_c_from_sparse_p_matches_live_reference():
 
 # ---------------------------------------------------------------------------------------------- TEASER++ front half
 def test_oracle_tims_follow_the_reference_segment_layout():
-    """UNPINNED restatement (no Eigen here): at least the layout rules the reference states in its own comments hold —
+    """The layout rules the reference states in its own comments —
     segment i starts at i*N - i*(i+1)/2, has N-1-i columns, and column c of it is v[:, i+1+c] - v[:, i] with map (i, j)
     (TEASER-plusplus/teaser/src/registration.cc:489-516); edges appear in that order and degrees count both ends."""
     rng = np.random.default_rng(5)
@@ -243,3 +243,33 @@ def test_oracle_tims_follow_the_reference_segment_layout():
     assert 0 < len(edges) < mask.size and (edges[:, 0] < edges[:, 1]).all()
     assert (np.diff(edges[:, 0] * N + edges[:, 1]) > 0).all()
     assert degree.sum() == 2 * len(edges)
+
+
+def _teaser_fixture():
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "teaser_golden.npz"))
+    n = g["src"].shape[1]
+    iu, ju = np.triu_indices(n, 1)
+    return g["src"], g["dst"], float(g["noise_bound"]), float(g["cbar2"]), g["inlier_matrix"], g["inlier_matrix"][iu, ju]
+
+
+def test_oracle_scale_inliers_match_the_reference_own_fixture():
+    """Pin: the reference's own test data for the fixed-scale problem (TEASER-plusplus/test/teaser/data/
+    registration_test/fixed_scale_inliers.csv, registration-test.cc:300-362) — 14028 TIMs, 2008 inliers, the closest
+    statistic 3e-5 away from beta — reproduced exactly by the restatement."""
+    src, dst, nb, cbar2, full, upper = _teaser_fixture()
+    edges, degree, mask = O.scale_inlier_graph(src, dst, nb, cbar2)
+    np.testing.assert_array_equal(mask, upper)
+    assert len(edges) == int(upper.sum()) == 2008
+    np.testing.assert_array_equal(degree, full.sum(1).astype(np.int32))
+
+
+def test_oracle_scale_inliers_known_answers_of_the_reference_test():
+    """ScaleSolverTest.FixedScale (TEASER-plusplus/test/teaser/scale-solver-test.cc:71-131) restated on its own data
+    (objectIn.csv): identical measurements -> all inliers; 3*v + 10 -> none; first column * 10 -> all but the first."""
+    obj = _teaser_fixture()[0]
+    assert O.scale_inliers(obj, obj, 1.0, 1).all()
+    assert not O.scale_inliers(obj, obj * 3 + 10, 1.0, 1).any()
+    shifted = obj.copy()
+    shifted[:, 0] *= 10
+    m = O.scale_inliers(obj, shifted, 1.0, 1)
+    assert not m[0] and m[1:].all()
