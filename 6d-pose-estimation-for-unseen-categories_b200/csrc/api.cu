@@ -57,6 +57,34 @@ int make_tensor_map_2d(CUtensorMap* map, const float* base, uint64_t cols, uint6
     return 0;
 }
 
+// ---- stage timing (bench.py's live per-kernel breakdown; off by default) -------------------------------
+struct StageState {
+    bool on = false, created = false;
+    cudaEvent_t ev[STAGE_MARKS];
+    bool have[STAGE_MARKS] = {};
+    std::vector<int*> cnt;
+};
+static StageState g_stage;
+static std::mutex g_stage_mu;
+bool stage_timing_on() { return g_stage.on; }
+static void stage_begin() {
+    if (!g_stage.on) return;
+    std::lock_guard<std::mutex> lk(g_stage_mu);
+    for (int i = 0; i < STAGE_MARKS; ++i) g_stage.have[i] = false;
+    g_stage.cnt.clear();
+}
+void stage_mark(int mark, cudaStream_t st) {
+    if (!g_stage.on || mark < 0 || mark >= STAGE_MARKS) return;
+    std::lock_guard<std::mutex> lk(g_stage_mu);
+    if (!g_stage.created) return;
+    if (cudaEventRecord(g_stage.ev[mark], st) == cudaSuccess) g_stage.have[mark] = true;
+}
+void stage_filter_counts(int* const* cnt_dev, int npairs) {
+    if (!g_stage.on) return;
+    std::lock_guard<std::mutex> lk(g_stage_mu);
+    g_stage.cnt.assign(cnt_dev, cnt_dev + npairs);
+}
+
 static int g_sm_count = 0;
 static int sm_count() {
     if (g_sm_count == 0) {
@@ -207,13 +235,18 @@ int f2p_naive_batched(const float* ex, const float* ey, const float* C, const F2
     unsigned char* ws = static_cast<unsigned char*>(ws_v);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     F2P_CUDA(cudaMemcpyAsync(ws + P.off_pairs, P.pairs.data(), sizeof(PairDev) * (size_t)npairs, cudaMemcpyHostToDevice, st));
+    stage_begin();
+    stage_mark(0, st);
     if ((rc = run_prep(P, ex, ey, C, npairs, k, ws, st))) return rc;
+    stage_mark(1, st);
     const PairDev* pd = reinterpret_cast<const PairDev*>(ws + P.off_pairs);
     ArgminWs aw;
     argmin_ws_carve(aw, ws + P.off_keys, P.ld2_total, k, npairs);
-    return launch_argmin(reinterpret_cast<float*>(ws + P.off_xT), P.ld1_total, reinterpret_cast<float*>(ws + P.off_nx),
+    rc = launch_argmin(reinterpret_cast<float*>(ws + P.off_xT), P.ld1_total, reinterpret_cast<float*>(ws + P.off_nx),
                          reinterpret_cast<float*>(ws + P.off_yT), P.ld2_total, reinterpret_cast<float*>(ws + P.off_ny), k, pd,
                          npairs, P.uni_items, P.total_items, P.uni_ytiles, P.total_ytiles, P.flops, flags, out, aw, st);
+    stage_mark(2, st);
+    return rc;
 }
 
 int f2p_spatial_batched(const float* ex, const float* ey, const float* C, const float* cad, const float* pc,
@@ -228,7 +261,10 @@ int f2p_spatial_batched(const float* ex, const float* ey, const float* C, const 
     unsigned char* ws = static_cast<unsigned char*>(ws_v);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     F2P_CUDA(cudaMemcpyAsync(ws + P.off_pairs, P.pairs.data(), sizeof(PairDev) * (size_t)npairs, cudaMemcpyHostToDevice, st));
+    stage_begin();
+    stage_mark(0, st);
     if ((rc = run_prep(P, ex, ey, C, npairs, k, ws, st))) return rc;
+    stage_mark(1, st);
     const PairDev* pd = reinterpret_cast<const PairDev*>(ws + P.off_pairs);
     u64* part5 = reinterpret_cast<u64*>(ws + P.off_keys);
     // candidates: caller's buffer uses the `out` layout (out_off, [2][5*n2]); the internal one is packed by cand0
@@ -238,8 +274,44 @@ int f2p_spatial_batched(const float* ex, const float* ey, const float* C, const 
                      npairs, P.uni_items, P.total_items, P.uni_ytiles, P.total_ytiles, flags, part5, cand,
                      cand_dev != nullptr, st);
     if (rc) return rc;
+    stage_mark(2, st);
     return run_filter_batch(P.pairs.data(), npairs, cad, pc, cand, cand_dev != nullptr, out, counts, status,
                             ws + P.off_fpairs, ws, P.filter_off.data(), st);
+}
+
+int f2p_stage_timing(int enable) {
+    std::lock_guard<std::mutex> lk(g_stage_mu);
+    if (enable && !g_stage.created) {
+        for (int i = 0; i < STAGE_MARKS; ++i) F2P_CUDA(cudaEventCreate(&g_stage.ev[i]));
+        g_stage.created = true;
+    }
+    g_stage.on = enable != 0;
+    for (int i = 0; i < STAGE_MARKS; ++i) g_stage.have[i] = false;
+    g_stage.cnt.clear();
+    return 0;
+}
+
+int f2p_stage_times(float* ms, double* filter_evals) {
+    if (!ms) { set_error("null pointer"); return F2P_EINVAL; }
+    std::lock_guard<std::mutex> lk(g_stage_mu);
+    for (int i = 0; i < STAGE_MARKS - 1; ++i) ms[i] = 0.f;
+    if (filter_evals) *filter_evals = 0.0;
+    if (!g_stage.created || !g_stage.have[0]) { set_error("no timed call recorded (f2p_stage_timing(1) first)"); return F2P_EINVAL; }
+    int last = 0;
+    for (int i = 0; i < STAGE_MARKS; ++i) if (g_stage.have[i]) last = i;
+    F2P_CUDA(cudaEventSynchronize(g_stage.ev[last]));
+    for (int i = 0; i + 1 < STAGE_MARKS; ++i)
+        if (g_stage.have[i] && g_stage.have[i + 1]) F2P_CUDA(cudaEventElapsedTime(&ms[i], g_stage.ev[i], g_stage.ev[i + 1]));
+    if (filter_evals) {
+        double s = 0.0;
+        for (int* p : g_stage.cnt) {
+            int c[3];
+            F2P_CUDA(cudaMemcpy(c, p, sizeof(c), cudaMemcpyDeviceToHost));
+            for (int r = 0; r < 3; ++r) s += (double)c[r] * (double)c[r];
+        }
+        *filter_evals = s;
+    }
+    return 0;
 }
 
 }  // extern "C"

@@ -65,6 +65,14 @@ int launch_top5(const float* xT, int64_t ld1_total, const float* nx, const float
 // filter.cu
 size_t filter_pair_bytes(int M);
 size_t filter_table_bytes(int npairs);
+// Optional stage timing of the batched entry points (api.cu; f2p_stage_timing / f2p_stage_times): marks are CUDA events
+// recorded on the caller's stream at the stage boundaries — 0 start, 1 projection done, 2 kernel 2 done, 3 filter init
+// done, then (vote, combine) of rounds 0..2 = marks 4..9.  No-ops unless timing is enabled.
+constexpr int STAGE_MARKS = 10;
+bool stage_timing_on();
+void stage_mark(int mark, cudaStream_t st);
+void stage_filter_counts(int* const* cnt_dev, int npairs);   // where each pair's round counts live (cnt[0..2])
+
 int run_filter_batch(const PairDev* pairs_host, int npairs, const float* cad, const float* pc, const int64_t* cand,
                      int cand_is_out_layout, int64_t* out, int32_t* counts, int32_t* status,
                      unsigned char* table_dev, unsigned char* ws_base, const size_t* filter_off, cudaStream_t st);

@@ -334,7 +334,8 @@ def run_b200_arm(args, wl):
     if rank == 0 and world == 1 and args.workload == "large" and not args.no_extra:
         line["other_workloads"] = side_workloads()
     if rank == 0:
-        line["roofline"] = roofline_section(L, _lib, wl, dev)
+        stages = stage_breakdown(L, _lib, step_resident, flush, max(2, min(args.steps, 5)))
+        line["roofline"] = roofline_section(L, _lib, wl, dev, ppg, stages)
         if not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
             cpu_reference_sample(wl, base[0], threads, 1)
@@ -392,9 +393,34 @@ def _traffic(wl):
     return None
 
 
-def roofline_section(L, _lib, wl, dev):
+STAGE_NAMES = ("projection", "kernel2", "filter_init", "vote0", "combine0", "vote1", "combine1", "vote2", "combine2")
+
+
+def stage_breakdown(L, _lib, step, flush, reps):
+    """Per-stage durations of the timed workload's own step: the library records CUDA events on the launching stream at
+    its stage boundaries (f2p_stage_timing / f2p_stage_times, include/f2p.h); L2 flushed before every step."""
+    ms = (ctypes.c_float * len(STAGE_NAMES))()
+    evals = ctypes.c_double(0)
+    acc = [0.0] * len(STAGE_NAMES)
+    _lib.check(L.f2p_stage_timing(1), "f2p_stage_timing")
+    try:
+        for _ in range(reps):
+            flush.fill_(1)
+            step()
+            _lib.check(L.f2p_stage_times(ms, ctypes.byref(evals)), "f2p_stage_times")
+            for i in range(len(acc)):
+                acc[i] += ms[i]
+    finally:
+        L.f2p_stage_timing(0)
+    return {"ms": {n: a / reps for n, a in zip(STAGE_NAMES, acc)}, "filter_evals_per_step": evals.value, "steps": reps,
+            "timed": "CUDA events recorded by the library on the launching stream at the stage boundaries of the timed "
+                     "step (f2p_stage_times)"}
+
+
+def roofline_section(L, _lib, wl, dev, ppg=1, stages=None):
     """Per-kernel rooflines measured live with CUDA events on the launching (current) stream.
-    Dominant kernel = kernel 2 (fused distance + argmin/top-5): FP32-pipe bound, algorithmic flops 2*n1*n2*k."""
+    Dominant kernel = kernel 2 (fused distance + argmin/top-5): FP32-pipe bound, algorithmic flops 2*n1*n2*k.
+    Batches: kernel 2 and the spatial filter are taken from the stage events of the batched step itself."""
     n1, n2, k = wl["n1"], wl["n2"], wl["k"]
     top5 = wl["solver"] == "spatial"
     P = gen_pair_fast(n1, n2, k, 99, False)
@@ -451,6 +477,30 @@ def roofline_section(L, _lib, wl, dev):
                        "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650 GB/s",
                        "flops_per_launch": 2.0 * n1 * k * k},
     }
+    if stages is not None:
+        sm = stages["ms"]
+        roof["stages"] = stages
+        if ppg > 1 and sm["kernel2"] > 0:
+            # the launch the step really makes: all pairs of the batch in one grid
+            roof["single_pair_launch"] = {"achieved": achieved, "frac": achieved / packed.value, "ms_per_launch": nm}
+            bat = flops * ppg / (sm["kernel2"] * 1e-3) / 1e12
+            roof.update({"achieved": bat, "frac": bat / packed.value, "frac_nominal": bat / NOMINAL_FP32_TFLOPS,
+                         "algorithmic_flops_per_launch": flops * ppg, "ms_per_launch": sm["kernel2"], "ms_best": None,
+                         "timed": stages["timed"] + ": %d pairs per launch" % ppg})
+        if top5 and stages["filter_evals_per_step"] > 0:
+            # kernel 3 = 21 flop per (a,b) evaluation of the reference x sum_r M_r^2, against the FP32 pipe
+            vote_ms = sm["vote0"] + sm["vote1"] + sm["vote2"]
+            comb_ms = sm["combine0"] + sm["combine1"] + sm["combine2"]
+            fl = 21.0 * stages["filter_evals_per_step"]
+            ach = fl / (vote_ms * 1e-3) / 1e12 if vote_ms > 0 else 0.0
+            roof["filter"] = {
+                "kernel": "vote_kernel (spatial-consistency vote, 3 rounds)", "bound": "fp32", "achieved": ach,
+                "peak": packed.value, "unit": "TFLOP/s", "frac": ach / packed.value,
+                "algorithmic_flops_per_step": fl, "evaluations_per_step": stages["filter_evals_per_step"],
+                "ms_vote": vote_ms, "ms_combine": comb_ms, "ms_init": sm["filter_init"],
+                "note": "reference work (both triangles, B per entry, every round); the kernel evaluates each unordered "
+                        "pair once, reuses B across the candidates of one scene point and skips a round whose "
+                        "predecessor pruned nothing, so the algorithmic rate may exceed the pipe peak"}
     return roof
 
 

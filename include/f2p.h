@@ -206,6 +206,17 @@ int f2p_spatial_host(const float* C_host, const float* evecs_x_host, int n1, con
  * runs ~ms of pure FMA work and returns TFLOP/s (roofline denominator next to the nominal figure). */
 int f2p_measure_fp32_peak(double* tflops_packed, double* tflops_scalar, void* stream);
 
+/* Stage timing of f2p_naive_batched / f2p_spatial_batched for the per-kernel roofline of bench.py (measurement aid; no
+ * reference counterpart).  Off by default; when on, the two entry points record CUDA events on the caller's stream at
+ * their stage boundaries (one timed call at a time).  f2p_stage_times waits for the last timed call and returns
+ *   ms[0] projection (both sides, norms fused)   ms[1] kernel 2 (key fill + gated arg-min / top-5 + finalise)
+ *   ms[2] filter init   ms[3], ms[5], ms[7] vote of round 0, 1, 2   ms[4], ms[6], ms[8] combine of round 0, 1, 2
+ * (zeros for stages the call did not run) and *filter_evals = sum over pairs and rounds of M_r^2, the (a,b) distance
+ * pair evaluations the reference performs for that batch (spacial_filtering.py:52-64; 0 for the naive solver). */
+#define F2P_STAGE_SLOTS 9
+int f2p_stage_timing(int enable);
+int f2p_stage_times(float ms[F2P_STAGE_SLOTS], double* filter_evals);
+
 #ifdef __cplusplus
 }
 #endif

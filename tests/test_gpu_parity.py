@@ -707,3 +707,38 @@ def test_teaser_front_matches_the_reference_own_fixture(solvers):
     np.testing.assert_array_equal(mask, full[iu, ju])
     np.testing.assert_array_equal(edges, np.stack([iu, ju], 1)[full[iu, ju]].astype(np.int32))
     np.testing.assert_array_equal(degree, full.sum(1).astype(np.int32))
+
+
+# ---------------------------------------------------------------------------------------------- stage timing aid
+@pytest.mark.gpu
+def test_stage_timing_reports_stages_and_leaves_results_unchanged(solvers, oracle):
+    """f2p_stage_timing / f2p_stage_times (bench.py's per-kernel breakdown): every stage of a spatial batch gets a
+    duration, filter_evals = sum_r M_r^2 is bracketed by the candidate and survivor counts, results are untouched."""
+    from fmap2pointmap_solvers import _lib
+    from fmap2pointmap_solvers.batched import naive_batched, spatial_batched
+    from fmap2pointmap_solvers.synth import make_pair
+    L = _lib.load()
+    P = [make_pair(700, 260, 30, seed=950 + i) for i in range(3)]
+    st = lambda name: torch.stack([getattr(p, name) for p in P], 0).cuda()   # noqa: E731
+    C, ex, ey, cad, pc = st("C12"), st("evecs_x"), st("evecs_y"), st("CAD"), st("PC")
+    diam = [p.diam_cad for p in P]
+    ms = (ctypes.c_float * 9)()
+    ev = ctypes.c_double(-1.0)
+    assert L.f2p_stage_times(ms, ctypes.byref(ev)) != 0          # nothing recorded yet: an error, not stale numbers
+    _lib.check(L.f2p_stage_timing(1), "f2p_stage_timing")
+    try:
+        res = spatial_batched(C, ex, ey, cad, pc, diam, verbose=False)
+        _lib.check(L.f2p_stage_times(ms, ctypes.byref(ev)), "f2p_stage_times")
+        t = list(ms)
+        assert all(x >= 0.0 for x in t) and t[0] > 0 and t[1] > 0 and t[3] > 0 and t[4] > 0
+        M0 = 5 * 260
+        surv = sum(int(r.shape[1]) ** 2 for r in res)
+        assert 3 * len(P) * M0 * M0 >= ev.value >= len(P) * M0 * M0 + 2 * surv      # M0 >= M1 >= M2 >= M'
+        got = naive_batched(C, ex, ey)
+        _lib.check(L.f2p_stage_times(ms, ctypes.byref(ev)), "f2p_stage_times")
+        assert ms[0] > 0 and ms[1] > 0 and all(ms[i] == 0 for i in range(2, 9)) and ev.value == 0
+    finally:
+        _lib.check(L.f2p_stage_timing(0), "f2p_stage_timing")
+    for i, p in enumerate(P):
+        np.testing.assert_array_equal(res[i].cpu().numpy(), oracle.spatial(p.C12, p.evecs_x, p.evecs_y, p.CAD, p.PC, diam[i]))
+        np.testing.assert_array_equal(got[i].cpu().numpy(), oracle.naive(p.C12, p.evecs_x, p.evecs_y, int16_compat=False))
