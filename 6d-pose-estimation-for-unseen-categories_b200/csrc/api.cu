@@ -291,25 +291,27 @@ int f2p_stage_timing(int enable) {
     return 0;
 }
 
-int f2p_stage_times(float* ms, double* filter_evals) {
+int f2p_stage_times(float* ms, double* filter_evals, double* ambiguous_cols) {
     if (!ms) { set_error("null pointer"); return F2P_EINVAL; }
     std::lock_guard<std::mutex> lk(g_stage_mu);
     for (int i = 0; i < STAGE_MARKS - 1; ++i) ms[i] = 0.f;
     if (filter_evals) *filter_evals = 0.0;
+    if (ambiguous_cols) *ambiguous_cols = 0.0;
     if (!g_stage.created || !g_stage.have[0]) { set_error("no timed call recorded (f2p_stage_timing(1) first)"); return F2P_EINVAL; }
     int last = 0;
     for (int i = 0; i < STAGE_MARKS; ++i) if (g_stage.have[i]) last = i;
     F2P_CUDA(cudaEventSynchronize(g_stage.ev[last]));
     for (int i = 0; i + 1 < STAGE_MARKS; ++i)
         if (g_stage.have[i] && g_stage.have[i + 1]) F2P_CUDA(cudaEventElapsedTime(&ms[i], g_stage.ev[i], g_stage.ev[i + 1]));
-    if (filter_evals) {
-        double s = 0.0;
+    if (filter_evals || ambiguous_cols) {
+        double s = 0.0, amb = 0.0;
         for (int* p : g_stage.cnt) {
-            int c[3];
+            int c[9];
             F2P_CUDA(cudaMemcpy(c, p, sizeof(c), cudaMemcpyDeviceToHost));
-            for (int r = 0; r < 3; ++r) s += (double)c[r] * (double)c[r];
+            for (int r = 0; r < 3; ++r) { s += (double)c[r] * (double)c[r]; amb += (double)c[6 + r]; }
         }
-        *filter_evals = s;
+        if (filter_evals) *filter_evals = s;
+        if (ambiguous_cols) *ambiguous_cols = amb;
     }
     return 0;
 }

@@ -87,7 +87,7 @@ _SIGNATURES = {
     "f2p_compute_tims": (ctypes.c_int, [_c_vp, ctypes.c_int, _c_vp, _c_vp, _c_vp]),
     "f2p_measure_fp32_peak": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), _c_vp]),
     "f2p_stage_timing": (ctypes.c_int, [ctypes.c_int]),
-    "f2p_stage_times": (ctypes.c_int, [ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_double)]),
+    "f2p_stage_times": (ctypes.c_int, [ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]),
 }
 
 _lib = None

@@ -400,19 +400,19 @@ def stage_breakdown(L, _lib, step, flush, reps):
     """Per-stage durations of the timed workload's own step: the library records CUDA events on the launching stream at
     its stage boundaries (f2p_stage_timing / f2p_stage_times, include/f2p.h); L2 flushed before every step."""
     ms = (ctypes.c_float * len(STAGE_NAMES))()
-    evals = ctypes.c_double(0)
+    evals, amb = ctypes.c_double(0), ctypes.c_double(0)
     acc = [0.0] * len(STAGE_NAMES)
     _lib.check(L.f2p_stage_timing(1), "f2p_stage_timing")
     try:
         for _ in range(reps):
             flush.fill_(1)
             step()
-            _lib.check(L.f2p_stage_times(ms, ctypes.byref(evals)), "f2p_stage_times")
+            _lib.check(L.f2p_stage_times(ms, ctypes.byref(evals), ctypes.byref(amb)), "f2p_stage_times")
             for i in range(len(acc)):
                 acc[i] += ms[i]
     finally:
         L.f2p_stage_timing(0)
-    return {"ms": {n: a / reps for n, a in zip(STAGE_NAMES, acc)}, "filter_evals_per_step": evals.value, "steps": reps,
+    return {"ms": {n: a / reps for n, a in zip(STAGE_NAMES, acc)}, "filter_evals_per_step": evals.value, "ambiguous_columns_per_step": amb.value, "steps": reps,
             "timed": "CUDA events recorded by the library on the launching stream at the stage boundaries of the timed "
                      "step (f2p_stage_times)"}
 
@@ -497,6 +497,7 @@ def roofline_section(L, _lib, wl, dev, ppg=1, stages=None):
                 "kernel": "vote_kernel (spatial-consistency vote, 3 rounds)", "bound": "fp32", "achieved": ach,
                 "peak": packed.value, "unit": "TFLOP/s", "frac": ach / packed.value,
                 "algorithmic_flops_per_step": fl, "evaluations_per_step": stages["filter_evals_per_step"],
+                "ambiguous_columns_per_step": stages["ambiguous_columns_per_step"],
                 "ms_vote": vote_ms, "ms_combine": comb_ms, "ms_init": sm["filter_init"],
                 "note": "reference work (both triangles, B per entry, every round); the kernel evaluates each unordered "
                         "pair once, reuses B across the candidates of one scene point and skips a round whose "

@@ -212,10 +212,12 @@ int f2p_measure_fp32_peak(double* tflops_packed, double* tflops_scalar, void* st
  *   ms[0] projection (both sides, norms fused)   ms[1] kernel 2 (key fill + gated arg-min / top-5 + finalise)
  *   ms[2] filter init   ms[3], ms[5], ms[7] vote of round 0, 1, 2   ms[4], ms[6], ms[8] combine of round 0, 1, 2
  * (zeros for stages the call did not run) and *filter_evals = sum over pairs and rounds of M_r^2, the (a,b) distance
- * pair evaluations the reference performs for that batch (spacial_filtering.py:52-64; 0 for the naive solver). */
+ * pair evaluations the reference performs for that batch (spacial_filtering.py:52-64; 0 for the naive solver), and
+ * *ambiguous_cols = columns (summed over pairs and rounds) whose screened score fell inside the error band of a threshold
+ * and were decided by the ordered arithmetic instead (csrc/filter.cu).  Either pointer may be NULL. */
 #define F2P_STAGE_SLOTS 9
 int f2p_stage_timing(int enable);
-int f2p_stage_times(float ms[F2P_STAGE_SLOTS], double* filter_evals);
+int f2p_stage_times(float ms[F2P_STAGE_SLOTS], double* filter_evals, double* ambiguous_cols);
 
 #ifdef __cplusplus
 }

@@ -724,18 +724,18 @@ def test_stage_timing_reports_stages_and_leaves_results_unchanged(solvers, oracl
     diam = [p.diam_cad for p in P]
     ms = (ctypes.c_float * 9)()
     ev = ctypes.c_double(-1.0)
-    assert L.f2p_stage_times(ms, ctypes.byref(ev)) != 0          # nothing recorded yet: an error, not stale numbers
+    assert L.f2p_stage_times(ms, ctypes.byref(ev), None) != 0          # nothing recorded yet: an error, not stale numbers
     _lib.check(L.f2p_stage_timing(1), "f2p_stage_timing")
     try:
         res = spatial_batched(C, ex, ey, cad, pc, diam, verbose=False)
-        _lib.check(L.f2p_stage_times(ms, ctypes.byref(ev)), "f2p_stage_times")
+        _lib.check(L.f2p_stage_times(ms, ctypes.byref(ev), None), "f2p_stage_times")
         t = list(ms)
         assert all(x >= 0.0 for x in t) and t[0] > 0 and t[1] > 0 and t[3] > 0 and t[4] > 0
         M0 = 5 * 260
         surv = sum(int(r.shape[1]) ** 2 for r in res)
         assert 3 * len(P) * M0 * M0 >= ev.value >= len(P) * M0 * M0 + 2 * surv      # M0 >= M1 >= M2 >= M'
         got = naive_batched(C, ex, ey)
-        _lib.check(L.f2p_stage_times(ms, ctypes.byref(ev)), "f2p_stage_times")
+        _lib.check(L.f2p_stage_times(ms, ctypes.byref(ev), None), "f2p_stage_times")
         assert ms[0] > 0 and ms[1] > 0 and all(ms[i] == 0 for i in range(2, 9)) and ev.value == 0
     finally:
         _lib.check(L.f2p_stage_timing(0), "f2p_stage_timing")

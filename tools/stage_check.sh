@@ -10,6 +10,6 @@ import json
 for w in ("batch","pair","large"):
     d=json.loads(open("gpurun_out/${T}_%s.json"%w).read().strip().splitlines()[-1]); r=d["roofline"]
     print(w, "ms/step=%.3f pairs/s=%.0f e2e=%.1f k2: %.2f TF frac=%.3f ms=%.4f"%(d["ms_per_step"], d["pairs_per_s"], d["e2e"]["pairs_per_s"], r["achieved"], r["frac"], r["ms_per_launch"]))
-    print("   stages", {k: round(v,4) for k,v in r["stages"]["ms"].items()}, "evals", r["stages"]["filter_evals_per_step"])
+    print("   stages", {k: round(v,4) for k,v in r["stages"]["ms"].items()}, "evals", r["stages"]["filter_evals_per_step"], "amb", r["stages"]["ambiguous_columns_per_step"])
     if "filter" in r: print("   filter", {k:(round(v,4) if isinstance(v,float) else v) for k,v in r["filter"].items() if k!="note"})
 PY
