@@ -215,6 +215,10 @@ int f2p_measure_fp32_peak(double* tflops_packed, double* tflops_scalar, void* st
  * pair evaluations the reference performs for that batch (spacial_filtering.py:52-64; 0 for the naive solver), and
  * *ambiguous_cols = columns (summed over pairs and rounds) whose screened score fell inside the error band of a threshold
  * and were decided by the ordered arithmetic instead (csrc/filter.cu).  Either pointer may be NULL. */
+/* Test hook: worst relative error of the screened vote's square root (sqrt.approx.ftz.f32) over the `count` floats
+ * with bit patterns first_bits, first_bits + stride, ...; the error band of csrc/filter.cu assumes <= 2^-21. */
+int f2p_test_sqrt_approx_error(uint32_t first_bits, uint32_t count, uint32_t stride, double* max_rel_err, void* stream);
+
 #define F2P_STAGE_SLOTS 9
 int f2p_stage_timing(int enable);
 int f2p_stage_times(float ms[F2P_STAGE_SLOTS], double* filter_evals, double* ambiguous_cols);

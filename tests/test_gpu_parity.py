@@ -742,3 +742,129 @@ def test_stage_timing_reports_stages_and_leaves_results_unchanged(solvers, oracl
     for i, p in enumerate(P):
         np.testing.assert_array_equal(res[i].cpu().numpy(), oracle.spatial(p.C12, p.evecs_x, p.evecs_y, p.CAD, p.PC, diam[i]))
         np.testing.assert_array_equal(got[i].cpu().numpy(), oracle.naive(p.C12, p.evecs_x, p.evecs_y, int16_compat=False))
+
+
+# ---------------------------------------------------------------------------------------------- screened vote
+def _filter_call(L, _lib, CAD, PC, p, thr4, want_scores=False):
+    """f2p_spatial_filter on one candidate list with caller-chosen thresholds -> (survivor columns [2,M'], status)."""
+    M = p.shape[1]
+    thr = (ctypes.c_float * 4)(*[float(t) for t in thr4])
+    out = torch.zeros(2, max(M, 1), dtype=torch.int64, device="cuda")
+    meta = torch.zeros(2, dtype=torch.int32, device="cuda")
+    scores = torch.full((3, max(M, 1)), float("nan"), device="cuda") if want_scores else None
+    ws = _ws(L.f2p_filter_workspace_bytes(M))
+    cd, pd, pp = CAD.cuda(), PC.cuda(), p.cuda()
+    rc = L.f2p_spatial_filter(cd.data_ptr(), CAD.shape[0], pd.data_ptr(), PC.shape[0], pp.data_ptr(), M, thr, out.data_ptr(),
+                              meta.data_ptr(), meta.data_ptr() + 4, None, scores.data_ptr() if want_scores else None,
+                              ws.data_ptr(), ws.numel(), None)
+    _lib.check(rc, "f2p_spatial_filter")
+    torch.cuda.synchronize()
+    m = int(meta[0])
+    return out.flatten()[:2 * m].view(2, m).cpu().numpy(), int(meta[1])
+
+
+def _oracle_filter_with_thresholds(oracle, X, Y, pick):
+    """The reference's three rounds (spacial_filtering.py:51-75) on gathered points, with every round's threshold chosen
+    by `pick(scores)` from that round's exact scores.  Returns (kept original columns, the four thresholds)."""
+    idx = np.arange(X.shape[0])
+    thr = []
+    for r in range(2):
+        s = oracle.vote_scores(X[idx], Y[idx])
+        t = pick(s, r)
+        thr.append(t)
+        idx = idx[s < t]
+    s = oracle.vote_scores(X[idx], Y[idx])
+    t2 = pick(s, 2)
+    t3 = np.nextafter(t2, np.float32(np.inf)) if len(s) else t2
+    keep = s < t2
+    if keep.sum() == 0:
+        keep = s < t3
+    return idx[keep], thr + [t2, t3]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M", [700, 2309, 4099])
+@pytest.mark.parametrize("mode", ["at_score", "next_up", "lowest"])
+def test_screened_vote_thresholds_on_exact_scores(solvers, oracle, M, mode):
+    """Thresholds placed exactly ON a column's reference score (s < thr false for it, true one ulp higher) or on the
+    lowest score (empty -> 0.065 fallback): the screened vote must hand these columns to the ordered arithmetic."""
+    from fmap2pointmap_solvers import _lib
+    L = _lib.load()
+    g = torch.Generator().manual_seed(4000 + M)
+    ncad, npc = 3 * M + 7, M + 3
+    CAD = torch.rand(ncad, 3, generator=g) * 10
+    p0 = torch.randint(0, ncad, (M,), generator=g)
+    p1 = torch.sort(torch.randint(0, npc, (M,), generator=g)).values
+    PC = torch.rand(npc, 3, generator=g) * 10
+    good = torch.rand(M, generator=g) < 0.6
+    Rm = torch.linalg.qr(torch.randn(3, 3, generator=g)).Q
+    PC[p1[good]] = CAD[p0[good]] @ Rm.t() + 0.05 * torch.randn(int(good.sum()), 3, generator=g)
+    p = torch.stack([p0, p1], 0).contiguous()
+    X, Y = CAD[p0].numpy(), PC[p1].numpy()
+
+    def pick(s, r):
+        if mode == "lowest" and r == 2:
+            return np.float32(s.min())                       # nothing below: the fallback threshold decides
+        t = np.float32(np.sort(s)[(2 * len(s)) // 3])
+        return np.nextafter(t, np.float32(np.inf)) if mode == "next_up" else t
+
+    kept, thr = _oracle_filter_with_thresholds(oracle, X, Y, pick)
+    got, status = _filter_call(L, _lib, CAD, PC, p, thr)
+    np.testing.assert_array_equal(got, p.numpy()[:, kept])
+    exact, _ = _filter_call(L, _lib, CAD, PC, p, thr, want_scores=True)      # the ordered path agrees as well
+    np.testing.assert_array_equal(exact, got)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M", [640, 1500])
+def test_screened_vote_all_columns_inside_the_band(solvers, oracle, M):
+    """Regular polygons: every column has the same real score, the FP32 scores differ by rounding only, so with the
+    threshold on the median score EVERY column is ambiguous and the whole round is decided by the verify pass."""
+    from fmap2pointmap_solvers import _lib
+    L = _lib.load()
+    ang = torch.arange(M, dtype=torch.float64) * (2 * np.pi / M)
+    # centred away from the origin: a coordinate like 5*cos(pi/2) ~ 3e-16 would send the pair to the ordered kernel
+    CAD = torch.stack([20 + 5 * torch.cos(ang), 30 + 5 * torch.sin(ang), torch.zeros(M, dtype=torch.float64)], 1).float()
+    PC = torch.stack([20 + 5.3 * torch.cos(ang), 30 + 5.3 * torch.sin(ang), torch.ones(M, dtype=torch.float64)], 1).float()
+    p = torch.stack([torch.arange(M), torch.arange(M)], 0).contiguous()
+    X, Y = CAD.numpy(), PC.numpy()
+    kept, thr = _oracle_filter_with_thresholds(oracle, X, Y, lambda s, r: np.float32(np.median(s)))
+    assert 0 < len(kept) < M
+    got, _ = _filter_call(L, _lib, CAD, PC, p, thr)
+    np.testing.assert_array_equal(got, p.numpy()[:, kept])
+
+
+@pytest.mark.gpu
+def test_screened_vote_sqrt_approx_error_bound():
+    """The error band of the screened vote (csrc/filter.cu) allows MUFU.SQRT a relative error of 2^-21: measured
+    exhaustively over every float a squared distance can be, [2^-100, FLT_MAX]."""
+    from fmap2pointmap_solvers import _lib
+    L = _lib.load()
+    first, last = 0x0D800000, 0x7F7FFFFF
+    err = ctypes.c_double(-1.0)
+    _lib.check(L.f2p_test_sqrt_approx_error(first, last - first + 1, 1, ctypes.byref(err), None), "f2p_test_sqrt_approx_error")
+    print("sqrt.approx.ftz.f32 max relative error: 2^%.2f" % np.log2(err.value))
+    assert 0.0 < err.value <= 2.0 ** -21
+    zero = ctypes.c_double(-1.0)
+    _lib.check(L.f2p_test_sqrt_approx_error(0, 1, 1, ctypes.byref(zero), None), "f2p_test_sqrt_approx_error")
+    assert not (zero.value > 0)                              # sqrt(0) = 0 exactly (0/0 -> NaN compares false)
+
+
+@pytest.mark.gpu
+def test_screened_vote_band_is_what_protects_the_result(solvers, oracle, monkeypatch):
+    """Negative control: with the error band forced to zero the screened scores decide alone, and on the all-ambiguous
+    polygon case they pick a different survivor set than the reference; with the proven band they match it."""
+    from fmap2pointmap_solvers import _lib
+    L = _lib.load()
+    M = 1500
+    ang = torch.arange(M, dtype=torch.float64) * (2 * np.pi / M)
+    CAD = torch.stack([20 + 5 * torch.cos(ang), 30 + 5 * torch.sin(ang), torch.zeros(M, dtype=torch.float64)], 1).float()
+    PC = torch.stack([20 + 5.3 * torch.cos(ang), 30 + 5.3 * torch.sin(ang), torch.ones(M, dtype=torch.float64)], 1).float()
+    p = torch.stack([torch.arange(M), torch.arange(M)], 0).contiguous()
+    kept, thr = _oracle_filter_with_thresholds(oracle, CAD.numpy(), PC.numpy(), lambda s, r: np.float32(np.median(s)))
+    monkeypatch.setenv("F2P_VOTE_BAND", "0")
+    unprotected, _ = _filter_call(L, _lib, CAD, PC, p, thr)
+    monkeypatch.delenv("F2P_VOTE_BAND")
+    protected, _ = _filter_call(L, _lib, CAD, PC, p, thr)
+    np.testing.assert_array_equal(protected, p.numpy()[:, kept])
+    assert unprotected.shape != protected.shape or (unprotected != protected).any()
