@@ -40,9 +40,16 @@ def _pinned(tag, shape, dtype):
 
 
 def _groups(n, chunks):
+    """Pair groups [lo, hi): `chunks` equal groups, the first one split again into a quarter and three quarters — the
+    first upload is the only one no kernel can hide, so it is kept short (a quarter of a group)."""
     chunks = max(1, min(int(chunks), n))
     step = (n + chunks - 1) // chunks
-    return [(lo, min(n, lo + step)) for lo in range(0, n, step)]
+    groups = [(lo, min(n, lo + step)) for lo in range(0, n, step)]
+    lo, hi = groups[0]
+    head = (hi - lo) // 4
+    if len(groups) > 1 and head >= 8:
+        groups[0:1] = [(lo, lo + head), (lo + head, hi)]
+    return groups
 
 
 def _check_host(*ts):

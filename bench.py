@@ -328,8 +328,8 @@ def run_b200_arm(args, wl):
         "clocks": clocks,
     }
     # kernels of this library launched per step (projection with fused norms 2; naive: init + gated arg-min + finalise 3;
-    # spatial: gated top-5 + exact fallback + finalise 3, filter init + 3 x (vote + combine) 7)
-    line["gpu_launches"] = (12 if spatial else 5) * args.steps
+    # spatial: gated top-5 + exact fallback + finalise 3, filter init + 3 x (vote + classify + verify + combine) 13)
+    line["gpu_launches"] = (18 if spatial else 5) * args.steps
 
     if rank == 0 and world == 1 and args.workload == "large" and not args.no_extra:
         line["other_workloads"] = side_workloads()

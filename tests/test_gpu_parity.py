@@ -637,14 +637,14 @@ def test_teaser_front_tims_and_scale_inlier_graph(solvers, oracle, n):
 
 # ---------------------------------------------------------------------------------------------- pipelined host batches
 @pytest.mark.gpu
-@pytest.mark.parametrize("chunks", [1, 3, 16])
-def test_host_pipelined_batches_match_one_shot_calls(solvers, oracle, chunks):
+@pytest.mark.parametrize("chunks,P", [(1, 7), (3, 7), (16, 7), (2, 70)])
+def test_host_pipelined_batches_match_one_shot_calls(solvers, oracle, chunks, P):
     """Stacked HOST batches cut into pair groups (H2D / kernels / D2H on three streams) give the very same maps as the
     one-shot device call, for both solvers, with pinned and pageable inputs and a C shared by the batch."""
     from fmap2pointmap_solvers.batched import naive_batched, spatial_batched
     from fmap2pointmap_solvers.pipeline import naive_host_pipelined, spatial_host_pipelined
     g = torch.Generator().manual_seed(31)
-    P, n1, n2, k = 7, 300, 130, 20
+    n1, n2, k = 300, 130, 20                 # P = 70 in two chunks: the first group is split again (short first upload)
     ex = torch.randn(P, n1, k, generator=g)
     ey = torch.randn(P, n2, k, generator=g)
     C = torch.eye(k).repeat(P, 1, 1) + 0.05 * torch.randn(P, k, k, generator=g)
