@@ -1,0 +1,164 @@
+"""GPU parity at BASELINE.json's FULL sizes (run on the B200 box with `-m gpu`).
+
+The oracle cannot materialise these cases whole in test time, so they are checked
+  * against the oracle on column blocks (the reference's `cdist` bits do not depend on how either operand is chunked,
+    SURVEY 8(a).1-3, so a block of scene points against ALL CAD rows is the reference's answer for those points), and
+  * through size-independent properties: chunk invariance (the whole call equals the concatenation of calls on column
+    slices), row-split merge (the winner over all CAD rows is the (distance, index)-least of the winners over row
+    slices), batch invariance (a pair's result does not depend on the batch around it), and the int16 wrap of row 1.
+cfg4 = configs[3]: one 100k x 100k pair, k = 128, naive.  cfg3 = configs[2]: 4096 pairs of 5k x 2k, k = 50, spatial.
+"""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def solvers():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import fmap2pointmap_solvers as S
+    from fmap2pointmap_solvers import _lib
+    _lib.load()  # must load the in-tree CUDA library: no fallback exists
+    return S
+
+
+@pytest.fixture(scope="module")
+def oracle():
+    from oracle import f2p_oracle as O
+    return O
+
+
+# ---------------------------------------------------------------------------------------------- cfg4
+@pytest.fixture(scope="module")
+def cfg4(solvers):
+    from fmap2pointmap_solvers.synth import make_pair
+    p = make_pair(100_000, 100_000, 128, seed=4242)
+    dev = {k: getattr(p, k).cuda() for k in ("C12", "evecs_x", "evecs_y")}
+    full = solvers.naive_fmap2pointmap(dev["C12"], dev["evecs_x"], dev["evecs_y"])
+    return p, dev, full
+
+
+def test_cfg4_full_size_column_blocks_vs_oracle(solvers, oracle, cfg4):
+    """100k x 100k x 128: first / last (ragged 32-column tail tile) / scattered scene points against the oracle over
+    ALL 100k CAD rows, bit-exact indices."""
+    p, dev, full = cfg4
+    assert full.dtype == torch.int64 and tuple(full.shape) == (2, 100_000)
+    got = full.cpu().numpy()
+    np.testing.assert_array_equal(got[1], np.arange(100_000))           # default row 1: the true point index
+    feat_x = oracle.project(p.evecs_x, p.C12)
+    rng = np.random.default_rng(7)
+    cols = np.unique(np.concatenate([np.arange(0, 768), np.arange(100_000 - 544, 100_000),
+                                     rng.choice(100_000, 1024, replace=False)]))
+    want = oracle.nn_argmin(feat_x, p.evecs_y.numpy()[cols])
+    np.testing.assert_array_equal(got[0, cols], want)
+    # the construction plants a true match for 70 % of the scene points: most arg-mins hit it (sanity of the workload)
+    planted = p.perm.numpy()
+    ok = planted >= 0
+    assert (got[0, ok] == planted[ok]).mean() > 0.5
+
+
+def test_cfg4_full_size_column_chunk_invariance(solvers, cfg4):
+    """The result for a scene point does not depend on which other scene points share the call (different column
+    tiles, row splits and TMA boxes): three uneven column slices concatenated equal the whole call."""
+    p, dev, full = cfg4
+    cuts = [0, 33_333, 50_001, 100_000]
+    parts = [solvers.naive_fmap2pointmap(dev["C12"], dev["evecs_x"], dev["evecs_y"][a:b])[0]
+             for a, b in zip(cuts[:-1], cuts[1:])]
+    assert torch.equal(torch.cat(parts), full[0])
+
+
+def test_cfg4_full_size_row_split_merge(solvers, oracle, cfg4):
+    """Winner over all CAD rows = (distance, index)-least of the winners over two row slices.  Distances of the slice
+    winners come from the oracle's per-pair distance (the reference's arithmetic), so the merge is exact."""
+    p, dev, full = cfg4
+    cut = 41_984 + 57                                             # not a multiple of the 128-row tile
+    lo = solvers.naive_fmap2pointmap(dev["C12"], dev["evecs_x"][:cut], dev["evecs_y"])[0].cpu().numpy()
+    hi = solvers.naive_fmap2pointmap(dev["C12"], dev["evecs_x"][cut:], dev["evecs_y"])[0].cpu().numpy() + cut
+    feat_x = oracle.project(p.evecs_x, p.C12)
+    ey = p.evecs_y.numpy()
+    jj = np.arange(100_000)
+    _, d_lo = oracle.pair_dist(feat_x, ey, lo, jj)
+    _, d_hi = oracle.pair_dist(feat_x, ey, hi, jj)
+    merged = np.where(d_hi < d_lo, hi, lo)                        # ties go to the lower index (the lower slice)
+    np.testing.assert_array_equal(full[0].cpu().numpy(), merged)
+
+
+def test_cfg4_full_size_int16_compat_row1(solvers, cfg4):
+    """`int16_compat=True` reproduces the reference's wrap of row 1 for V2 > 32767 (naive.py:21); row 0 is unchanged."""
+    p, dev, full = cfg4
+    got = solvers.naive_fmap2pointmap(dev["C12"], dev["evecs_x"], dev["evecs_y"], int16_compat=True)
+    assert torch.equal(got[0], full[0])
+    want = torch.linspace(0, 99_999, 100_000).type(torch.int16).to(torch.int64)
+    assert torch.equal(got[1].cpu(), want)
+
+
+# ---------------------------------------------------------------------------------------------- cfg3
+N_DISTINCT, SCALES = 16, (1.0, 1.7, 2.5, 4.0)
+
+
+@pytest.fixture(scope="module")
+def cfg3_inputs(solvers):
+    """4096 pairs of 5k x 2k x 50: 16 distinct seeded pairs in a shuffled order, each occurrence with one of four
+    CAD diameters (so the filter's thresholds, round counts and branches differ between the occurrences)."""
+    from fmap2pointmap_solvers.synth import make_pair
+    P = 4096
+    base = [make_pair(5000, 2000, 50, seed=1234 + i) for i in range(N_DISTINCT)]
+    g = torch.Generator().manual_seed(99)
+    which = torch.randint(0, N_DISTINCT, (P,), generator=g)
+    scale_id = torch.randint(0, len(SCALES), (P,), generator=g)
+    st = lambda name: torch.stack([getattr(b, name) for b in base], 0).cuda()   # noqa: E731
+    sel = which.cuda()
+    dev = {name: st(name).index_select(0, sel) for name in ("C12", "evecs_x", "evecs_y", "CAD", "PC")}
+    diam = [base[int(w)].diam_cad * SCALES[int(s)] for w, s in zip(which, scale_id)]
+    return base, which.numpy(), scale_id.numpy(), dev, diam
+
+
+def test_cfg3_full_batch_4096_pairs_spatial_vs_oracle(solvers, oracle, cfg3_inputs):
+    """configs[2] at its full size in ONE call: every one of the 4096 maps equals the oracle's map of its
+    (pair, diameter) combination — bit-exact indices, identical survivor sets."""
+    from fmap2pointmap_solvers.batched import spatial_batched
+    base, which, scale_id, dev, diam = cfg3_inputs
+    flat, counts, status = spatial_batched(dev["C12"], dev["evecs_x"], dev["evecs_y"], dev["CAD"], dev["PC"], diam,
+                                           verbose=False, packed=True)
+    torch.cuda.synchronize()
+    assert tuple(flat.shape) == (4096, 20_000)
+    counts_h, status_h = counts.cpu().numpy(), status.cpu().numpy()
+    assert not (status_h & 2).any()
+    want = {}
+    for w in range(N_DISTINCT):
+        b = base[w]
+        for s, sc in enumerate(SCALES):
+            want[(w, s)] = oracle.spatial(b.C12, b.evecs_x, b.evecs_y, b.CAD, b.PC, b.diam_cad * sc)
+    sizes = sorted({v.shape[1] for v in want.values()})
+    assert sizes[-1] > sizes[0]                                    # the diameters do change what survives
+    want_dev = {key: torch.from_numpy(v).cuda() for key, v in want.items()}
+    bad = []
+    for i in range(4096):
+        key = (int(which[i]), int(scale_id[i]))
+        m = want[key].shape[1]
+        if counts_h[i] != m or not torch.equal(flat[i, :2 * m].view(2, m), want_dev[key]):
+            bad.append(i)
+    assert not bad, f"{len(bad)} of 4096 pairs differ from the oracle, first: {bad[:8]}"
+
+
+def test_cfg3_full_batch_4096_pairs_naive_and_batch_invariance(solvers, oracle, cfg3_inputs):
+    """The naive solver over the same 4096-pair batch, and batch invariance of the spatial solver: a 64-pair slice
+    taken from the middle of the batch gives the same maps as inside the 4096-pair call."""
+    from fmap2pointmap_solvers.batched import naive_batched, spatial_batched
+    base, which, scale_id, dev, diam = cfg3_inputs
+    got = naive_batched(dev["C12"], dev["evecs_x"], dev["evecs_y"])
+    assert tuple(got.shape) == (4096, 2, 2000)
+    want = torch.stack([torch.from_numpy(oracle.naive(b.C12, b.evecs_x, b.evecs_y, int16_compat=False)) for b in base], 0).cuda()
+    assert torch.equal(got, want.index_select(0, torch.from_numpy(which).cuda()))
+    flat, counts, _ = spatial_batched(dev["C12"], dev["evecs_x"], dev["evecs_y"], dev["CAD"], dev["PC"], diam,
+                                      verbose=False, packed=True)
+    a, b = 2017, 2081
+    sl = spatial_batched(dev["C12"][a:b], dev["evecs_x"][a:b], dev["evecs_y"][a:b], dev["CAD"][a:b], dev["PC"][a:b],
+                         diam[a:b], verbose=False)
+    ch = counts.cpu().numpy()
+    for i, r in enumerate(sl):
+        m = int(ch[a + i])
+        assert r.shape[1] == m and torch.equal(r, flat[a + i, :2 * m].view(2, m))
