@@ -63,16 +63,14 @@ __device__ __forceinline__ float aten_sqnorm(const float* p, int64_t stride, int
 }
 
 // grid.x = total row tiles over all pairs (x operand) or column tiles (y operand).
-// smem: eT[k][EPAD] + Cs[2][k][8] (+ fT[k][EPAD] when C is given: the projected rows, kept for the fused norms)
+// Transpose only (the operand that is not projected): outT[c][col0+r] = e[r][c], norms of the rows as they are.
+// smem: eT[k][EPAD]
 template <bool IS_X>
 __global__ void __launch_bounds__(PREP_THREADS)
-project_kernel(const float* __restrict__ evecs, const float* __restrict__ Cmat, const PairDev* __restrict__ pairs,
-               int npairs, int uniform_tiles, int k, float* __restrict__ outT, int64_t ld_total,
-               float* __restrict__ nrm, int use_ft) {
+transpose_kernel(const float* __restrict__ evecs, const PairDev* __restrict__ pairs, int npairs, int uniform_tiles, int k,
+                 float* __restrict__ outT, int64_t ld_total, float* __restrict__ nrm) {
     extern __shared__ float smem[];
     float* eT = smem;                 // [k][EPAD]
-    float* Cs = smem + (((size_t)k * EPAD + 3) & ~(size_t)3);  // 2 x [k][8], 16-byte aligned
-    float* fT = Cs + (size_t)k * 16;  // [k][EPAD]
     const int tid = threadIdx.x;
     const int pi = find_pair(blockIdx.x, pairs, npairs, uniform_tiles, IS_X ? &PairDev::xtile0 : &PairDev::ytile0);
     const PairDev pd = pairs[pi];
@@ -90,76 +88,138 @@ project_kernel(const float* __restrict__ evecs, const float* __restrict__ Cmat, 
         eT[b * EPAD + r] = (gi < n) ? __ldg(src + (int64_t)gi * ldin + b) : 0.f;
     }
     __syncthreads();
-
     const int r = tid & (TILE - 1);
-    const int half = tid >> 7;  // 0/1: which of two interleaved 8-wide output chunks this thread computes
+    for (int c = tid >> 7; c < k; c += 2) outT[(int64_t)c * ld_total + col0 + r] = eT[c * EPAD + r];
+    // padding rows: +inf for the streamed operand so they never win, else 0
+    if (tid < TILE) nrm[col0 + tid] = (row0 + tid < n) ? aten_sqnorm(eT + tid, EPAD, k, 1.f) : (IS_X ? __int_as_float(0x7f800000) : 0.f);
+}
 
-    if (Cmat == nullptr) {
-        // transpose only: outT[c][col0+r] = e[r][c]
-        for (int c = half; c < k; c += 2) outT[(int64_t)c * ld_total + col0 + r] = eT[c * EPAD + r];
-        // norms of the rows as they are (padding rows: +inf for the streamed operand so they never win, else 0)
-        if (tid < TILE) nrm[col0 + tid] = (row0 + tid < n) ? aten_sqnorm(eT + tid, EPAD, k, 1.f) : (IS_X ? __int_as_float(0x7f800000) : 0.f);
-        return;
+// Projection: feat = e . C^T for a [TILE][k] tile of points, written k-major as -2*feat, with the fused row norms.
+// A register-tiled FP32 product: warp = 8 consecutive outputs a (one pass covers 8 warps x 8 = 64 outputs), lane = 4
+// consecutive points, 4 x 8 accumulators per thread held as packed pairs along a.  Every output keeps the reference's
+// chain — one accumulator, b ascending, fused multiply-add (`fma.rn.f32x2` = two independent IEEE FMAs).  Per b a
+// thread issues one LDS.128 of points (4 wavefronts per warp), two broadcast LDS.128 of C and 16 packed FMAs.
+// smem: eT[k][ELD] + Cs[k][CLD] (+ fT[k][ELD] when it fits: the projected rows, kept for the fused norms)
+constexpr int ELD = TILE + 4;   // float4-aligned rows; lane = (b & 7, r & 3) makes the transposing stores conflict-free
+constexpr int CLD = 64 + 4;     // one pass of outputs + pad (staging stores: 4-way conflicts instead of 32-way)
+
+template <bool IS_X>
+__global__ void __launch_bounds__(PREP_THREADS)
+project_kernel(const float* __restrict__ evecs, const float* __restrict__ Cmat, const PairDev* __restrict__ pairs,
+               int npairs, int uniform_tiles, int k, float* __restrict__ outT, int64_t ld_total,
+               float* __restrict__ nrm, int use_ft) {
+    extern __shared__ __align__(16) float smem[];
+    float* eT = smem;                          // [k][ELD]
+    float* Cs = eT + (size_t)k * ELD;          // [k][CLD]: Cs[b][q] = C[a0 + q][b]
+    float* fT = Cs + (size_t)k * CLD;          // [k][ELD]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int pi = find_pair(blockIdx.x, pairs, npairs, uniform_tiles, IS_X ? &PairDev::xtile0 : &PairDev::ytile0);
+    const PairDev pd = pairs[pi];
+    const int tile = blockIdx.x - (IS_X ? pd.xtile0 : pd.ytile0);
+    const int n = IS_X ? pd.n1 : pd.n2;
+    const int ldin = IS_X ? pd.ldx : pd.ldy;
+    const float* src = evecs + (IS_X ? pd.ex_off : pd.ey_off);
+    const int row0 = tile * TILE;
+    const int64_t col0 = (int64_t)(IS_X ? pd.x_col0 : pd.y_col0) + row0;
+
+    // [TILE][k] row-major tile -> eT[b][r]: a warp reads 8 consecutive b of 4 rows (whole 32-byte sectors)
+    const int nbc = (k + 7) >> 3;
+    for (int idx = tid; idx < TILE * 8 * nbc; idx += PREP_THREADS) {
+        const int rest = idx >> 5;
+        const int bc = rest % nbc, rb = rest / nbc;
+        const int b = bc * 8 + (idx & 7), r = rb * 4 + ((idx >> 3) & 3);
+        const int gi = row0 + r;
+        if (b < k) eT[b * ELD + r] = (gi < n) ? __ldg(src + (int64_t)gi * ldin + b) : 0.f;
     }
+
     const float* Cp = Cmat + pd.c_off;
-    for (int a0 = 0; a0 < k; a0 += 16) {
-        // stage Cs[h][b][q] = C[a0 + 8h + q][b] for both halves
-        __syncthreads();
-        for (int idx = tid; idx < 16 * k; idx += PREP_THREADS) {
+    const float* ep = eT + 4 * lane;
+    const float* cp = Cs + 8 * warp;
+    for (int a0 = 0; a0 < k; a0 += 64) {
+        __syncthreads();                       // eT complete / the previous pass has finished reading Cs
+        for (int idx = tid; idx < 64 * k; idx += PREP_THREADS) {
             const int q = idx / k, b = idx - q * k;
             const int a = a0 + q;
-            Cs[(q >> 3) * (k * 8) + b * 8 + (q & 7)] = (a < k) ? __ldg(Cp + (int64_t)a * k + b) : 0.f;
+            Cs[b * CLD + q] = (a < k) ? __ldg(Cp + (int64_t)a * k + b) : 0.f;
         }
         __syncthreads();
-        const float* Ch = Cs + half * (k * 8);
-        float acc[8];
+        const int aw = a0 + 8 * warp;          // this warp's 8 outputs
+        if (aw >= k) continue;
+        u64 acc[4][4];
 #pragma unroll
-        for (int q = 0; q < 8; ++q) acc[q] = 0.f;
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j] = 0ull;
+#pragma unroll 2
         for (int b = 0; b < k; ++b) {
-            const float e = eT[b * EPAD + r];
-            const float4 c0 = *reinterpret_cast<const float4*>(Ch + b * 8);
-            const float4 c1 = *reinterpret_cast<const float4*>(Ch + b * 8 + 4);
-            acc[0] = __fmaf_rn(e, c0.x, acc[0]); acc[1] = __fmaf_rn(e, c0.y, acc[1]);
-            acc[2] = __fmaf_rn(e, c0.z, acc[2]); acc[3] = __fmaf_rn(e, c0.w, acc[3]);
-            acc[4] = __fmaf_rn(e, c1.x, acc[4]); acc[5] = __fmaf_rn(e, c1.y, acc[5]);
-            acc[6] = __fmaf_rn(e, c1.z, acc[6]); acc[7] = __fmaf_rn(e, c1.w, acc[7]);
+            const float4 e = *reinterpret_cast<const float4*>(ep + b * ELD);
+            const ulonglong2 c0 = *reinterpret_cast<const ulonglong2*>(cp + b * CLD);
+            const ulonglong2 c1 = *reinterpret_cast<const ulonglong2*>(cp + b * CLD + 4);
+            const float ev[4] = {e.x, e.y, e.z, e.w};
+            const u64 cv[4] = {c0.x, c0.y, c1.x, c1.y};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const u64 ee = pack2(ev[i], ev[i]);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) fma2(acc[i][j], ee, cv[j]);
+            }
         }
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-            const int a = a0 + half * 8 + q;
-            if (a < k) { outT[(int64_t)a * ld_total + col0 + r] = -2.0f * acc[q]; if (use_ft) fT[a * EPAD + r] = acc[q]; }
+        for (int j = 0; j < 4; ++j) {
+            float lo[4], hi[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) unpack2(acc[i][j], lo[i], hi[i]);
+            const int a = aw + 2 * j;
+            if (a < k) {
+                *reinterpret_cast<float4*>(outT + (int64_t)a * ld_total + col0 + 4 * lane) =
+                    make_float4(-2.0f * lo[0], -2.0f * lo[1], -2.0f * lo[2], -2.0f * lo[3]);
+                if (use_ft) *reinterpret_cast<float4*>(fT + a * ELD + 4 * lane) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+            }
+            if (a + 1 < k) {
+                *reinterpret_cast<float4*>(outT + (int64_t)(a + 1) * ld_total + col0 + 4 * lane) =
+                    make_float4(-2.0f * hi[0], -2.0f * hi[1], -2.0f * hi[2], -2.0f * hi[3]);
+                if (use_ft) *reinterpret_cast<float4*>(fT + (a + 1) * ELD + 4 * lane) = make_float4(hi[0], hi[1], hi[2], hi[3]);
+            }
         }
     }
-    // fused row norms of the projected points: from the shared-memory copy, or (k too large for a second [k][129]
+    // fused row norms of the projected points: from the shared-memory copy, or (k too large for a second [k][ELD]
     // buffer) from this CTA's own stores, which the barrier makes visible
     __syncthreads();
     if (tid < TILE) {
         float v = IS_X ? __int_as_float(0x7f800000) : 0.f;
         if (row0 + tid < n)
-            v = use_ft ? aten_sqnorm(fT + tid, EPAD, k, 1.f) : aten_sqnorm(outT + col0 + tid, ld_total, k, -0.5f);
+            v = use_ft ? aten_sqnorm(fT + tid, ELD, k, 1.f) : aten_sqnorm(outT + col0 + tid, ld_total, k, -0.5f);
         nrm[col0 + tid] = v;
     }
 }
 
 // Host launchers -----------------------------------------------------------------------------------
+template <bool IS_X>
+static int launch_project_t(const float* evecs, const float* Cmat, const PairDev* pairs_dev, int npairs, int uniform_tiles,
+                            int total_tiles, int k, float* outT, int64_t ld_total, float* nrm, cudaStream_t stream) {
+    if (Cmat == nullptr) {
+        const size_t smem = (size_t)k * EPAD * sizeof(float);
+        static bool attr_done = false;
+        if (!attr_done) { F2P_CUDA(cudaFuncSetAttribute(transpose_kernel<IS_X>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024)); attr_done = true; }
+        transpose_kernel<IS_X><<<total_tiles, PREP_THREADS, smem, stream>>>(evecs, pairs_dev, npairs, uniform_tiles, k, outT, ld_total, nrm);
+    } else {
+        const size_t base = (size_t)k * (ELD + CLD) * sizeof(float);
+        const int use_ft = base + (size_t)k * ELD * sizeof(float) <= 112 * 1024;   // keep 2 CTAs per SM
+        const size_t smem = base + (use_ft ? (size_t)k * ELD * sizeof(float) : 0);
+        static bool attr_done = false;
+        if (!attr_done) { F2P_CUDA(cudaFuncSetAttribute(project_kernel<IS_X>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024)); attr_done = true; }
+        project_kernel<IS_X><<<total_tiles, PREP_THREADS, smem, stream>>>(evecs, Cmat, pairs_dev, npairs, uniform_tiles, k, outT, ld_total, nrm, use_ft);
+    }
+    F2P_CUDA(cudaGetLastError());
+    return 0;
+}
+
 int launch_project(bool is_x, const float* evecs, const float* Cmat, const PairDev* pairs_dev, int npairs,
                    int uniform_tiles, int total_tiles, int k, float* outT, int64_t ld_total, float* nrm,
                    cudaStream_t stream) {
     if (total_tiles <= 0) return 0;
-    const size_t base = ((((size_t)k * EPAD + 3) & ~(size_t)3) + (size_t)k * 16) * sizeof(float);
-    const int use_ft = Cmat && base + (size_t)k * EPAD * sizeof(float) <= 112 * 1024;   // keep 2 CTAs per SM
-    const size_t smem = base + (use_ft ? (size_t)k * EPAD * sizeof(float) : 0);
-    if (is_x) {
-        static bool attr_done = false;
-        if (!attr_done) { F2P_CUDA(cudaFuncSetAttribute(project_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024)); attr_done = true; }
-        project_kernel<true><<<total_tiles, PREP_THREADS, smem, stream>>>(evecs, Cmat, pairs_dev, npairs, uniform_tiles, k, outT, ld_total, nrm, use_ft);
-    } else {
-        static bool attr_done = false;
-        if (!attr_done) { F2P_CUDA(cudaFuncSetAttribute(project_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024)); attr_done = true; }
-        project_kernel<false><<<total_tiles, PREP_THREADS, smem, stream>>>(evecs, Cmat, pairs_dev, npairs, uniform_tiles, k, outT, ld_total, nrm, use_ft);
-    }
-    F2P_CUDA(cudaGetLastError());
-    return 0;
+    return is_x ? launch_project_t<true>(evecs, Cmat, pairs_dev, npairs, uniform_tiles, total_tiles, k, outT, ld_total, nrm, stream)
+                : launch_project_t<false>(evecs, Cmat, pairs_dev, npairs, uniform_tiles, total_tiles, k, outT, ld_total, nrm, stream);
 }
 
 }  // namespace f2p
