@@ -12,7 +12,7 @@
 namespace f2p {
 
 constexpr int PREP_THREADS = 256;
-constexpr int EPAD = TILE + 1;  // padded row of the transposed evecs tile: conflict-free transposed stores
+constexpr int ELD = TILE + 4;   // row of the transposed evecs tile: float4-aligned; the loader's lane mapping keeps stores conflict-free
 
 // ATen `x.pow(2).sum(-1)` of one point whose k values sit at p[c * stride]: 8 lanes x ILP-4 partial sums (k < 8: four
 // interleaved scalar chains), squares rounded first.  `scale` is an exact power of two (-0.5 recovers feat from -2*feat).
@@ -62,15 +62,38 @@ __device__ __forceinline__ float aten_sqnorm(const float* p, int64_t stride, int
     return f;
 }
 
+// 4-byte asynchronous global -> shared copy (LDGSTS): no register staging, so a thread keeps all its loads in flight;
+// `live == false` zero-fills the destination without reading the source.
+__device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc, bool live) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(live ? 4 : 0) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// [TILE][k] row-major tile of points -> eT[b][r] (row stride ELD), issued as asynchronous copies (the caller waits).
+// A warp reads 8 consecutive b of 4 consecutive rows per step (whole 32-byte sectors) and its 32 transposed stores hit
+// 32 different banks ((4*b + r) mod 32); warps walk 4-row blocks, lanes keep their (b, r) offsets: no integer
+// divisions, and every lane has its TILE*k/256 loads outstanding at once (a register-staged loop kept 4: the kernel
+// then ran at a quarter of the bytes in flight that HBM latency asks for).  Rows >= n are zero-filled.
+__device__ __forceinline__ void load_tile_T_async(float* eT, const float* __restrict__ src, int ldin, int row0, int n, int k) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int bl = lane & 7, rl = lane >> 3;
+    for (int rb = warp; rb < TILE / 4; rb += PREP_THREADS / 32) {
+        const int r = rb * 4 + rl, gi = row0 + r;
+        const bool live = gi < n;
+        const float* p = live ? src + (int64_t)gi * ldin : src;
+        for (int b = bl; b < k; b += 8) cp_async4(eT + b * ELD + r, p + b, live);
+    }
+}
+
 // grid.x = total row tiles over all pairs (x operand) or column tiles (y operand).
 // Transpose only (the operand that is not projected): outT[c][col0+r] = e[r][c], norms of the rows as they are.
-// smem: eT[k][EPAD]
+// smem: eT[k][ELD]
 template <bool IS_X>
 __global__ void __launch_bounds__(PREP_THREADS)
 transpose_kernel(const float* __restrict__ evecs, const PairDev* __restrict__ pairs, int npairs, int uniform_tiles, int k,
                  float* __restrict__ outT, int64_t ld_total, float* __restrict__ nrm) {
     extern __shared__ float smem[];
-    float* eT = smem;                 // [k][EPAD]
+    float* eT = smem;                 // [k][ELD]
     const int tid = threadIdx.x;
     const int pi = find_pair(blockIdx.x, pairs, npairs, uniform_tiles, IS_X ? &PairDev::xtile0 : &PairDev::ytile0);
     const PairDev pd = pairs[pi];
@@ -81,17 +104,13 @@ transpose_kernel(const float* __restrict__ evecs, const PairDev* __restrict__ pa
     const int row0 = tile * TILE;
     const int64_t col0 = (int64_t)(IS_X ? pd.x_col0 : pd.y_col0) + row0;
 
-    // coalesced read of the [TILE][k] row-major tile, transposed into smem
-    for (int idx = tid; idx < TILE * k; idx += PREP_THREADS) {
-        const int r = idx / k, b = idx - r * k;
-        const int gi = row0 + r;
-        eT[b * EPAD + r] = (gi < n) ? __ldg(src + (int64_t)gi * ldin + b) : 0.f;
-    }
+    load_tile_T_async(eT, src, ldin, row0, n, k);
+    cp_async_wait_all();
     __syncthreads();
     const int r = tid & (TILE - 1);
-    for (int c = tid >> 7; c < k; c += 2) outT[(int64_t)c * ld_total + col0 + r] = eT[c * EPAD + r];
+    for (int c = tid >> 7; c < k; c += 2) outT[(int64_t)c * ld_total + col0 + r] = eT[c * ELD + r];
     // padding rows: +inf for the streamed operand so they never win, else 0
-    if (tid < TILE) nrm[col0 + tid] = (row0 + tid < n) ? aten_sqnorm(eT + tid, EPAD, k, 1.f) : (IS_X ? __int_as_float(0x7f800000) : 0.f);
+    if (tid < TILE) nrm[col0 + tid] = (row0 + tid < n) ? aten_sqnorm(eT + tid, ELD, k, 1.f) : (IS_X ? __int_as_float(0x7f800000) : 0.f);
 }
 
 // Projection: feat = e . C^T for a [TILE][k] tile of points, written k-major as -2*feat, with the fused row norms.
@@ -100,7 +119,6 @@ transpose_kernel(const float* __restrict__ evecs, const PairDev* __restrict__ pa
 // chain — one accumulator, b ascending, fused multiply-add (`fma.rn.f32x2` = two independent IEEE FMAs).  Per b a
 // thread issues one LDS.128 of points (4 wavefronts per warp), two broadcast LDS.128 of C and 16 packed FMAs.
 // smem: eT[k][ELD] + Cs[k][CLD] (+ fT[k][ELD] when it fits: the projected rows, kept for the fused norms)
-constexpr int ELD = TILE + 4;   // float4-aligned rows; lane = (b & 7, r & 3) makes the transposing stores conflict-free
 constexpr int CLD = 64 + 4;     // one pass of outputs + pad (staging stores: 4-way conflicts instead of 32-way)
 
 template <bool IS_X>
@@ -122,26 +140,20 @@ project_kernel(const float* __restrict__ evecs, const float* __restrict__ Cmat, 
     const int row0 = tile * TILE;
     const int64_t col0 = (int64_t)(IS_X ? pd.x_col0 : pd.y_col0) + row0;
 
-    // [TILE][k] row-major tile -> eT[b][r]: a warp reads 8 consecutive b of 4 rows (whole 32-byte sectors)
-    const int nbc = (k + 7) >> 3;
-    for (int idx = tid; idx < TILE * 8 * nbc; idx += PREP_THREADS) {
-        const int rest = idx >> 5;
-        const int bc = rest % nbc, rb = rest / nbc;
-        const int b = bc * 8 + (idx & 7), r = rb * 4 + ((idx >> 3) & 3);
-        const int gi = row0 + r;
-        if (b < k) eT[b * ELD + r] = (gi < n) ? __ldg(src + (int64_t)gi * ldin + b) : 0.f;
-    }
+    load_tile_T_async(eT, src, ldin, row0, n, k);
 
     const float* Cp = Cmat + pd.c_off;
     const float* ep = eT + 4 * lane;
     const float* cp = Cs + 8 * warp;
     for (int a0 = 0; a0 < k; a0 += 64) {
-        __syncthreads();                       // eT complete / the previous pass has finished reading Cs
-        for (int idx = tid; idx < 64 * k; idx += PREP_THREADS) {
-            const int q = idx / k, b = idx - q * k;
+        if (a0) __syncthreads();               // the previous pass has finished reading Cs
+        for (int q = warp; q < 64; q += PREP_THREADS / 32) {      // warp = one row of C, lanes along b (no divisions)
             const int a = a0 + q;
-            Cs[b * CLD + q] = (a < k) ? __ldg(Cp + (int64_t)a * k + b) : 0.f;
+            const bool live = a < k;
+            const float* crow = live ? Cp + (int64_t)a * k : Cp;
+            for (int b = lane; b < k; b += 32) cp_async4(Cs + b * CLD + q, crow + b, live);
         }
+        cp_async_wait_all();                   // first pass: the point tile too
         __syncthreads();
         const int aw = a0 + 8 * warp;          // this warp's 8 outputs
         if (aw >= k) continue;
@@ -198,7 +210,7 @@ template <bool IS_X>
 static int launch_project_t(const float* evecs, const float* Cmat, const PairDev* pairs_dev, int npairs, int uniform_tiles,
                             int total_tiles, int k, float* outT, int64_t ld_total, float* nrm, cudaStream_t stream) {
     if (Cmat == nullptr) {
-        const size_t smem = (size_t)k * EPAD * sizeof(float);
+        const size_t smem = (size_t)k * ELD * sizeof(float);
         static bool attr_done = false;
         if (!attr_done) { F2P_CUDA(cudaFuncSetAttribute(transpose_kernel<IS_X>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024)); attr_done = true; }
         transpose_kernel<IS_X><<<total_tiles, PREP_THREADS, smem, stream>>>(evecs, pairs_dev, npairs, uniform_tiles, k, outT, ld_total, nrm);
