@@ -187,14 +187,14 @@ static int check_ws(const Plan& P, void* ws, size_t ws_bytes) {
 }
 
 // projection of both operands + norms for the whole batch
+// (one launch; `aw` non-null: also resets the arg-min merge keys and arrival counters of every column tile)
 static int run_prep(const Plan& P, const float* ex, const float* ey, const float* C, int npairs, int k,
-                    unsigned char* ws, cudaStream_t st) {
+                    unsigned char* ws, cudaStream_t st, const ArgminWs* aw = nullptr) {
     const PairDev* pd = reinterpret_cast<const PairDev*>(ws + P.off_pairs);
-    int rc = launch_project(true, ex, C, pd, npairs, P.uni_xtiles, P.total_xtiles, k,
-                            reinterpret_cast<float*>(ws + P.off_xT), P.ld1_total, reinterpret_cast<float*>(ws + P.off_nx), st);
-    if (rc) return rc;
-    return launch_project(false, ey, nullptr, pd, npairs, P.uni_ytiles, P.total_ytiles, k,
-                          reinterpret_cast<float*>(ws + P.off_yT), P.ld2_total, reinterpret_cast<float*>(ws + P.off_ny), st);
+    return launch_prep(ex, C, ey, pd, npairs, P.uni_xtiles, P.total_xtiles, P.uni_ytiles, P.total_ytiles, k,
+                       reinterpret_cast<float*>(ws + P.off_xT), P.ld1_total, reinterpret_cast<float*>(ws + P.off_nx),
+                       reinterpret_cast<float*>(ws + P.off_yT), P.ld2_total, reinterpret_cast<float*>(ws + P.off_ny),
+                       aw ? aw->best : nullptr, aw ? aw->tilecnt : nullptr, st);
 }
 
 }  // namespace f2p
@@ -237,14 +237,14 @@ int f2p_naive_batched(const float* ex, const float* ey, const float* C, const F2
     F2P_CUDA(cudaMemcpyAsync(ws + P.off_pairs, P.pairs.data(), sizeof(PairDev) * (size_t)npairs, cudaMemcpyHostToDevice, st));
     stage_begin();
     stage_mark(0, st);
-    if ((rc = run_prep(P, ex, ey, C, npairs, k, ws, st))) return rc;
-    stage_mark(1, st);
-    const PairDev* pd = reinterpret_cast<const PairDev*>(ws + P.off_pairs);
     ArgminWs aw;
     argmin_ws_carve(aw, ws + P.off_keys, P.ld2_total, k, npairs);
+    if ((rc = run_prep(P, ex, ey, C, npairs, k, ws, st, &aw))) return rc;
+    stage_mark(1, st);
+    const PairDev* pd = reinterpret_cast<const PairDev*>(ws + P.off_pairs);
     rc = launch_argmin(reinterpret_cast<float*>(ws + P.off_xT), P.ld1_total, reinterpret_cast<float*>(ws + P.off_nx),
                          reinterpret_cast<float*>(ws + P.off_yT), P.ld2_total, reinterpret_cast<float*>(ws + P.off_ny), k, pd,
-                         npairs, P.uni_items, P.total_items, P.uni_ytiles, P.total_ytiles, P.flops, flags, out, aw, st);
+                         npairs, P.uni_items, P.total_items, P.uni_ytiles, P.total_ytiles, P.flops, flags, out, aw, st, true);
     stage_mark(2, st);
     return rc;
 }

@@ -45,10 +45,15 @@ static inline int choose_nsplit(long long base_items, int nrt, int sm, int min_t
 int launch_project(bool is_x, const float* evecs, const float* Cmat, const PairDev* pairs_dev, int npairs,
                    int uniform_tiles, int total_tiles, int k, float* outT, int64_t ld_total, float* nrm,
                    cudaStream_t stream);
+// both operands in one launch; best_init / tilecnt (optional): arg-min merge keys and per-column-tile arrival counters,
+// reset by the CTAs that prepare the scene operand (then launch_argmin(..., pre_init = true) needs no init launch)
+int launch_prep(const float* ex, const float* Cmat, const float* ey, const PairDev* pairs_dev, int npairs, int uni_xtiles,
+                int total_xtiles, int uni_ytiles, int total_ytiles, int k, float* xT, int64_t ld1_total, float* nx,
+                float* yT, int64_t ld2_total, float* ny, unsigned long long* best_init, int* tilecnt, cudaStream_t stream);
 // nn.cu
 struct ArgminWs {
     unsigned long long* best; unsigned long long* best_exact; float* yTf; float* nyf;
-    uint32_t* best2; int* flagged; int* nflag;
+    uint32_t* best2; int* flagged; int* nflag; int* tilecnt;
 };
 size_t nn_smem_bytes(int k, int mode);
 size_t top5_ws_bytes(int64_t total_items, int64_t total_ytiles);
@@ -57,7 +62,7 @@ void argmin_ws_carve(ArgminWs& w, unsigned char* base, int64_t ld2_total, int k,
 int launch_argmin(const float* xT, int64_t ld1_total, const float* nx, const float* yT, int64_t ld2_total,
                   const float* ny, int k, const PairDev* pairs_dev, int npairs, int uniform_items, int total_items,
                   int uniform_ytiles, int total_ytiles, double flops, unsigned flags, int64_t* out, const ArgminWs& w,
-                  cudaStream_t stream);
+                  cudaStream_t stream, bool pre_init = false);
 int launch_top5(const float* xT, int64_t ld1_total, const float* nx, const float* yT, int64_t ld2_total, const float* ny,
                 int k, const PairDev* pairs_dev, int npairs, int uniform_items, int total_items, int uniform_ytiles,
                 int total_ytiles, unsigned flags, unsigned long long* part5, int64_t* cand, int cand_is_out_layout,

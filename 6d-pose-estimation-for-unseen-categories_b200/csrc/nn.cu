@@ -32,9 +32,17 @@ struct NNParams {
     const int* ncols;    // MODE 0 re-check pass: per-pair number of (compacted) columns to process, or null = n2
     int* tileflag;       // [total column tiles]: gated kernel sets 1 when a candidate list overflowed; MODE 0/1 launched
                          // as the exact fallback process only flagged column tiles (null = process everything)
+    int* tilecnt;        // gated arg-min, fused finalise: [total column tiles] arrival counters (pre-set to 0), or null
+    int64_t* out;        // fused finalise: the batch's int64 result buffer (PairDev::out_off)
+    unsigned flags;      // fused finalise: F2P_INT16_COMPAT / F2P_ROW0_ONLY
 };
 
 constexpr uint32_t IDX_NONE = 0x7fffffffu;
+
+__device__ __forceinline__ int64_t row1_value(int j, unsigned flags) {
+    // linspace(0,V2-1,V2).type(int16) promoted to int64 (naive.py:21): wraps modulo 2^16 on the reference's CPU path
+    return (flags & F2P_INT16_COMPAT) ? (int64_t)(int16_t)(uint16_t)(j & 0xffff) : (int64_t)j;
+}
 constexpr int PRODUCER_TID = NN_THREADS - 32;   // lane 0 of the last (highest-priority) warp issues all TMA loads
 
 __device__ __forceinline__ u64 make_key(float d, uint32_t i) {
@@ -393,7 +401,10 @@ __device__ __forceinline__ void gated_compact(int col, float* s_val, uint32_t* s
     if (m == K) s_tau[col] = raw[K - 1];
 }
 
-template <int K, int KC, int NSTAGE, int NXP>   // NXP: L1 prefetch of the row norms at tile start, load in the epilogue
+// NXP: L1 prefetch of the row norms at tile start, load in the epilogue.  FUSE (K == 1): the last CTA of a column tile
+// writes the int64 map itself (small problems, where a finalise launch is a tenth of the call); a separate instance so
+// that the plain kernel's register allocation — tuned at the 128-register cap — stays exactly as it was.
+template <int K, int KC, int NSTAGE, int NXP, int FUSE = 0>
 __global__ void __launch_bounds__(NN_THREADS, 2)
 nn_gated_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapY, const NNParams prm) {
     constexpr int CAP = GatedCfg<K>::CAP;
@@ -631,6 +642,28 @@ nn_gated_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
     if (K == 1) {
         __syncthreads();
         if (tid < TILE && ct * TILE + tid < pd_n2) atomicMin(prm.best + ycol + tid, s_best[tid]);
+        if (FUSE) {
+            // fused finalise (saves a launch): the last of this column tile's row-split CTAs to arrive turns the merged
+            // keys into the int64 map.  Release: every thread's atomicMin, fence, barrier, then one counter increment;
+            // acquire: the CTA that reads nsplit-1 fences and reads the keys from L2, where the atomics were performed.
+            // The pair fields are looked up again here rather than kept live across the main loop (128-register cap).
+            __threadfence();
+            __syncthreads();
+            const int it2 = blockIdx.x;
+            const PairDev* q = prm.pairs + find_pair(it2, prm.pairs, prm.npairs, prm.uniform_items, &PairDev::item0);
+            const int ns2 = q->nsplit, ct2 = (it2 - q->item0) / ns2;
+            if (tid == 0) *s_ovf = (atomicAdd(prm.tilecnt + q->ytile0 + ct2, 1) == ns2 - 1);
+            __syncthreads();
+            const int j = ct2 * TILE + tid, n2 = q->n2;
+            if (*s_ovf && tid < TILE && j < n2) {
+                __threadfence();
+                uint32_t idx = (uint32_t)(__ldcg(prm.best + q->y_col0 + j) & 0xffffffffull);
+                if (idx >= IDX_NONE) idx = 0;  // all distances were +inf/NaN: out of contract, mirror argmin's first index
+                int64_t* o = prm.out + q->out_off;
+                o[j] = (int64_t)idx;
+                if (!(prm.flags & F2P_ROW0_ONLY)) o[(int64_t)n2 + j] = row1_value(j, prm.flags);
+            }
+        }
     } else {
         if (tid < TILE) {
 #pragma unroll
@@ -643,11 +676,6 @@ nn_gated_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
 }
 
 // ---- finalize: keys -> int64 index maps ---------------------------------------------------------------
-__device__ __forceinline__ int64_t row1_value(int j, unsigned flags) {
-    // linspace(0,V2-1,V2).type(int16) promoted to int64 (naive.py:21): wraps modulo 2^16 on the reference's CPU path
-    return (flags & F2P_INT16_COMPAT) ? (int64_t)(int16_t)(uint16_t)(j & 0xffff) : (int64_t)j;
-}
-
 // grid.x = total column tiles; one thread per column.  out[pair] = int64 [2,n2].
 __global__ void __launch_bounds__(TILE)
 finalize_argmin_kernel(const u64* __restrict__ best, const PairDev* __restrict__ pairs, int npairs, int uniform_tiles,
@@ -830,7 +858,10 @@ static int launch_gated_kc(const float* xT, int64_t ld1_total, const float* yT, 
     const char* ep = getenv("F2P_GATED_NXP");
     const int nxp = ep ? atoi(ep) : (K == 1 ? 1 : 0);
     const size_t smem = gated_smem_bytes<K>(k, KCV, NSTAGE);
-    if (nxp) {
+    if (K == 1 && prm.tilecnt) {
+        F2P_CUDA(cudaFuncSetAttribute(nn_gated_kernel<1, KCV, NSTAGE, 1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        nn_gated_kernel<1, KCV, NSTAGE, 1, 1><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);
+    } else if (nxp) {
         F2P_CUDA(cudaFuncSetAttribute(nn_gated_kernel<K, KCV, NSTAGE, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         nn_gated_kernel<K, KCV, NSTAGE, 1><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);
     } else {
@@ -860,6 +891,7 @@ size_t argmin_ws_bytes(int64_t ld2_total, int k, int npairs) {
     b += n * sizeof(int);                       // flagged
     b += n * sizeof(float);                     // nyf
     b += ((size_t)(npairs > 0 ? npairs : 1) * sizeof(int) + 255) & ~(size_t)255;   // nflag
+    b += ((n / TILE + 1) * sizeof(int) + 255) & ~(size_t)255;                        // tilecnt
     b += (size_t)k * n * sizeof(float);         // yTf
     return (b + 255) & ~(size_t)255;
 }
@@ -873,7 +905,8 @@ void argmin_ws_carve(ArgminWs& w, unsigned char* base, int64_t ld2_total, int k,
     w.nyf = reinterpret_cast<float*>(p); p += n * sizeof(float);
     w.best2 = reinterpret_cast<uint32_t*>(p); p += n * sizeof(uint32_t);
     w.flagged = reinterpret_cast<int*>(p); p += n * sizeof(int);
-    w.nflag = reinterpret_cast<int*>(p);
+    w.nflag = reinterpret_cast<int*>(p); p += ((size_t)(npairs > 0 ? npairs : 1) * sizeof(int) + 255) & ~(size_t)255;
+    w.tilecnt = reinterpret_cast<int*>(p);
 }
 
 // Path switch (tests): F2P_NN_PATH = "exact" (nn_kernel<0/1> alone), "two_phase" (arg-min: raw pass + re-check of
@@ -886,21 +919,30 @@ static NNPath nn_path() {
     return PATH_GATED;
 }
 
+constexpr int FUSE_MAX_ITEMS = 16 * 148;   // ~8 waves of 2 CTAs per SM on a B200
+
 int launch_argmin(const float* xT, int64_t ld1_total, const float* nx, const float* yT, int64_t ld2_total,
                   const float* ny, int k, const PairDev* pairs_dev, int npairs, int uniform_items, int total_items,
                   int uniform_ytiles, int total_ytiles, double flops, unsigned flags, int64_t* out, const ArgminWs& w,
-                  cudaStream_t stream) {
+                  cudaStream_t stream, bool pre_init) {
     if (total_items <= 0 || total_ytiles <= 0) return 0;
     NNParams prm;
     prm.pairs = pairs_dev; prm.npairs = npairs; prm.uniform_items = uniform_items; prm.k = k;
     prm.nx = nx; prm.ny = ny; prm.best = w.best; prm.part5 = nullptr; prm.best2 = nullptr; prm.ncols = nullptr;
-    prm.tileflag = nullptr;
+    prm.tileflag = nullptr; prm.tilecnt = nullptr; prm.out = out; prm.flags = flags;
     const NNPath path = nn_path();
     (void)flops;
     const unsigned iblocks = (unsigned)((ld2_total + 255) / 256);
     int rc;
+    if (path == PATH_GATED && pre_init && total_items <= FUSE_MAX_ITEMS) {
+        // small problem (a few waves): keys and arrival counters were reset by launch_prep, the kernel finalises its own
+        // column tiles — one launch instead of three
+        prm.tilecnt = w.tilecnt;
+        return launch_gated<1>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
+    }
     if (path == PATH_GATED) {
-        argmin_init_kernel<<<iblocks, 256, 0, stream>>>(w.best, nullptr, nullptr, (size_t)ld2_total, nullptr, 0, nullptr);
+        if (!pre_init)
+            argmin_init_kernel<<<iblocks, 256, 0, stream>>>(w.best, nullptr, nullptr, (size_t)ld2_total, nullptr, 0, nullptr);
         if ((rc = launch_gated<1>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream))) return rc;   // exact, no fallback
         finalize_argmin_kernel<<<total_ytiles, TILE, 0, stream>>>(w.best, pairs_dev, npairs, uniform_ytiles, flags, out);
         F2P_CUDA(cudaGetLastError());
@@ -936,7 +978,7 @@ int launch_top5(const float* xT, int64_t ld1_total, const float* nx, const float
     NNParams prm;
     prm.pairs = pairs_dev; prm.npairs = npairs; prm.uniform_items = uniform_items; prm.k = k;
     prm.nx = nx; prm.ny = ny; prm.best = nullptr; prm.part5 = part5; prm.best2 = nullptr; prm.ncols = nullptr;
-    prm.tileflag = nullptr;
+    prm.tileflag = nullptr; prm.tilecnt = nullptr; prm.out = nullptr; prm.flags = flags;
     int rc;
     if (nn_path() == PATH_GATED) {
         // tile flags follow the partial lists in the workspace (top5_ws_bytes)

@@ -89,15 +89,15 @@ __device__ __forceinline__ void load_tile_T_async(float* eT, const float* __rest
 // Transpose only (the operand that is not projected): outT[c][col0+r] = e[r][c], norms of the rows as they are.
 // smem: eT[k][ELD]
 template <bool IS_X>
-__global__ void __launch_bounds__(PREP_THREADS)
-transpose_kernel(const float* __restrict__ evecs, const PairDev* __restrict__ pairs, int npairs, int uniform_tiles, int k,
-                 float* __restrict__ outT, int64_t ld_total, float* __restrict__ nrm) {
-    extern __shared__ float smem[];
+__device__ __forceinline__ void
+transpose_body(int bid, float* smem, const float* __restrict__ evecs, const PairDev* __restrict__ pairs, int npairs,
+               int uniform_tiles, int k, float* __restrict__ outT, int64_t ld_total, float* __restrict__ nrm,
+               u64* __restrict__ best_init, int* __restrict__ tilecnt) {
     float* eT = smem;                 // [k][ELD]
     const int tid = threadIdx.x;
-    const int pi = find_pair(blockIdx.x, pairs, npairs, uniform_tiles, IS_X ? &PairDev::xtile0 : &PairDev::ytile0);
+    const int pi = find_pair(bid, pairs, npairs, uniform_tiles, IS_X ? &PairDev::xtile0 : &PairDev::ytile0);
     const PairDev pd = pairs[pi];
-    const int tile = blockIdx.x - (IS_X ? pd.xtile0 : pd.ytile0);
+    const int tile = bid - (IS_X ? pd.xtile0 : pd.ytile0);
     const int n = IS_X ? pd.n1 : pd.n2;
     const int ldin = IS_X ? pd.ldx : pd.ldy;
     const float* src = evecs + (IS_X ? pd.ex_off : pd.ey_off);
@@ -111,6 +111,17 @@ transpose_kernel(const float* __restrict__ evecs, const PairDev* __restrict__ pa
     for (int c = tid >> 7; c < k; c += 2) outT[(int64_t)c * ld_total + col0 + r] = eT[c * ELD + r];
     // padding rows: +inf for the streamed operand so they never win, else 0
     if (tid < TILE) nrm[col0 + tid] = (row0 + tid < n) ? aten_sqnorm(eT + tid, ELD, k, 1.f) : (IS_X ? __int_as_float(0x7f800000) : 0.f);
+    // fused arg-min state of this column tile (saves the init launch of kernel 2): merge keys and the arrival counter
+    if (best_init && tid >= TILE) best_init[col0 + tid - TILE] = ~0ull;
+    if (tilecnt && tid == 0) tilecnt[bid] = 0;
+}
+
+template <bool IS_X>
+__global__ void __launch_bounds__(PREP_THREADS)
+transpose_kernel(const float* __restrict__ evecs, const PairDev* __restrict__ pairs, int npairs, int uniform_tiles, int k,
+                 float* __restrict__ outT, int64_t ld_total, float* __restrict__ nrm) {
+    extern __shared__ __align__(16) float smem[];
+    transpose_body<IS_X>(blockIdx.x, smem, evecs, pairs, npairs, uniform_tiles, k, outT, ld_total, nrm, nullptr, nullptr);
 }
 
 // Projection: feat = e . C^T for a [TILE][k] tile of points, written k-major as -2*feat, with the fused row norms.
@@ -122,18 +133,17 @@ transpose_kernel(const float* __restrict__ evecs, const PairDev* __restrict__ pa
 constexpr int CLD = 64 + 4;     // one pass of outputs + pad (staging stores: 4-way conflicts instead of 32-way)
 
 template <bool IS_X>
-__global__ void __launch_bounds__(PREP_THREADS)
-project_kernel(const float* __restrict__ evecs, const float* __restrict__ Cmat, const PairDev* __restrict__ pairs,
-               int npairs, int uniform_tiles, int k, float* __restrict__ outT, int64_t ld_total,
-               float* __restrict__ nrm, int use_ft) {
-    extern __shared__ __align__(16) float smem[];
+__device__ __forceinline__ void
+project_body(int bid, float* smem, const float* __restrict__ evecs, const float* __restrict__ Cmat,
+             const PairDev* __restrict__ pairs, int npairs, int uniform_tiles, int k, float* __restrict__ outT,
+             int64_t ld_total, float* __restrict__ nrm, int use_ft) {
     float* eT = smem;                          // [k][ELD]
     float* Cs = eT + (size_t)k * ELD;          // [k][CLD]: Cs[b][q] = C[a0 + q][b]
     float* fT = Cs + (size_t)k * CLD;          // [k][ELD]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int pi = find_pair(blockIdx.x, pairs, npairs, uniform_tiles, IS_X ? &PairDev::xtile0 : &PairDev::ytile0);
+    const int pi = find_pair(bid, pairs, npairs, uniform_tiles, IS_X ? &PairDev::xtile0 : &PairDev::ytile0);
     const PairDev pd = pairs[pi];
-    const int tile = blockIdx.x - (IS_X ? pd.xtile0 : pd.ytile0);
+    const int tile = bid - (IS_X ? pd.xtile0 : pd.ytile0);
     const int n = IS_X ? pd.n1 : pd.n2;
     const int ldin = IS_X ? pd.ldx : pd.ldy;
     const float* src = evecs + (IS_X ? pd.ex_off : pd.ey_off);
@@ -205,6 +215,31 @@ project_kernel(const float* __restrict__ evecs, const float* __restrict__ Cmat, 
     }
 }
 
+template <bool IS_X>
+__global__ void __launch_bounds__(PREP_THREADS)
+project_kernel(const float* __restrict__ evecs, const float* __restrict__ Cmat, const PairDev* __restrict__ pairs,
+               int npairs, int uniform_tiles, int k, float* __restrict__ outT, int64_t ld_total,
+               float* __restrict__ nrm, int use_ft) {
+    extern __shared__ __align__(16) float smem[];
+    project_body<IS_X>(blockIdx.x, smem, evecs, Cmat, pairs, npairs, uniform_tiles, k, outT, ld_total, nrm, use_ft);
+}
+
+// Both operands of a batch in ONE launch: CTAs [0, total_xtiles) project the CAD eigenbasis, the rest transpose the scene
+// eigenbasis (and reset the arg-min merge state of their column tile).  A single 5k x 2k pair is 5 short kernels; each
+// launch boundary costs ~2.5 us of drain + launch latency next to ~15 us of work.
+__global__ void __launch_bounds__(PREP_THREADS)
+prep_kernel(const float* __restrict__ ex, const float* __restrict__ Cmat, const float* __restrict__ ey,
+            const PairDev* __restrict__ pairs, int npairs, int uni_xtiles, int total_xtiles, int uni_ytiles, int k,
+            float* __restrict__ xT, int64_t ld1_total, float* __restrict__ nx, float* __restrict__ yT, int64_t ld2_total,
+            float* __restrict__ ny, int use_ft, u64* __restrict__ best_init, int* __restrict__ tilecnt) {
+    extern __shared__ __align__(16) float smem[];
+    if ((int)blockIdx.x < total_xtiles)
+        project_body<true>(blockIdx.x, smem, ex, Cmat, pairs, npairs, uni_xtiles, k, xT, ld1_total, nx, use_ft);
+    else
+        transpose_body<false>(blockIdx.x - total_xtiles, smem, ey, pairs, npairs, uni_ytiles, k, yT, ld2_total, ny,
+                              best_init, tilecnt);
+}
+
 // Host launchers -----------------------------------------------------------------------------------
 template <bool IS_X>
 static int launch_project_t(const float* evecs, const float* Cmat, const PairDev* pairs_dev, int npairs, int uniform_tiles,
@@ -222,6 +257,21 @@ static int launch_project_t(const float* evecs, const float* Cmat, const PairDev
         if (!attr_done) { F2P_CUDA(cudaFuncSetAttribute(project_kernel<IS_X>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024)); attr_done = true; }
         project_kernel<IS_X><<<total_tiles, PREP_THREADS, smem, stream>>>(evecs, Cmat, pairs_dev, npairs, uniform_tiles, k, outT, ld_total, nrm, use_ft);
     }
+    F2P_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int launch_prep(const float* ex, const float* Cmat, const float* ey, const PairDev* pairs_dev, int npairs, int uni_xtiles,
+                int total_xtiles, int uni_ytiles, int total_ytiles, int k, float* xT, int64_t ld1_total, float* nx,
+                float* yT, int64_t ld2_total, float* ny, unsigned long long* best_init, int* tilecnt, cudaStream_t stream) {
+    if (total_xtiles + total_ytiles <= 0) return 0;
+    const size_t base = (size_t)k * (ELD + CLD) * sizeof(float);
+    const int use_ft = base + (size_t)k * ELD * sizeof(float) <= 112 * 1024;   // keep 2 CTAs per SM
+    const size_t smem = base + (use_ft ? (size_t)k * ELD * sizeof(float) : 0);
+    static bool attr_done = false;
+    if (!attr_done) { F2P_CUDA(cudaFuncSetAttribute(prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024)); attr_done = true; }
+    prep_kernel<<<total_xtiles + total_ytiles, PREP_THREADS, smem, stream>>>(ex, Cmat, ey, pairs_dev, npairs, uni_xtiles,
+        total_xtiles, uni_ytiles, k, xT, ld1_total, nx, yT, ld2_total, ny, use_ft, best_init, tilecnt);
     F2P_CUDA(cudaGetLastError());
     return 0;
 }
