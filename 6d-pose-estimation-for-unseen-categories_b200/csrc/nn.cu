@@ -583,7 +583,42 @@ nn_gated_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
 
         if (t == 0) {
             // bootstrap (tau = +inf): bounded appends per cut so the first tile cannot overflow
-            if (K == 1) {
+            if (K == 1 && FUSE) {
+                // Small problems run 2-3 row tiles per CTA, so this first tile is a third of the work: one square root
+                // per column instead of one per element.  cm = the column's raw minimum over the 32 rows of the 4 lanes
+                // that share it, s = sqrt_rn(cm), tau' = up((s + 1ulp)^2): a row ties or beats s exactly when its raw
+                // value is below tau' (then sqrt_rn(c) <= s, and c >= cm gives sqrt_rn(c) >= s), and the lowest such
+                // row index is the reference's winner.  (Tried in the plain instance at 100k x 100k x 128: the extra
+                // live values cost the main loop registers there; this instance only serves small problems.)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    float c[8];
+                    float cm = INF;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        float v0, v1;
+                        unpack2(add2(add2(acc[i][j >> 1], pack2(nxv[i], nxv[i])), ny2[j >> 1]), v0, v1);
+                        c[i] = fmaxf((j & 1) ? v1 : v0, 0.f);
+                        cm = fminf(cm, c[i]);
+                    }
+                    cm = fminf(cm, __shfl_xor_sync(0xffffffffu, cm, 8));
+                    cm = fminf(cm, __shfl_xor_sync(0xffffffffu, cm, 16));
+                    const float sr = __fsqrt_rn(cm);
+                    const float su = __uint_as_float(__float_as_uint(sr) + 1u);
+                    const float tn = __fmul_ru(su, su);
+                    uint32_t bi = IDX_NONE;
+#pragma unroll
+                    for (int i = 7; i >= 0; --i)
+                        if (c[i] < tn) bi = (uint32_t)(rowbase + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4)));
+                    bi = min(bi, __shfl_xor_sync(0xffffffffu, bi, 8));
+                    bi = min(bi, __shfl_xor_sync(0xffffffffu, bi, 16));
+                    if ((lane & 24) == 0 && bi != IDX_NONE) {
+                        const int col = j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4);
+                        atomicMin(s_best + col, make_key(sr, bi));
+                        atomicMin(reinterpret_cast<unsigned*>(s_tau) + col, __float_as_uint(tn));
+                    }
+                }
+            } else if (K == 1) {
                 // exact local arg-min over this thread's 8 rows, merged across the 4 lanes sharing a column
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
