@@ -457,6 +457,10 @@ nn_gated_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
         if (K == 1) s_best[tid] = ~0ull; else s_cnt[tid] = 0;
     }
     __syncthreads();
+    // Small-problem instance: launched with programmatic stream serialization behind the preparation kernel, so the
+    // launch latency and the prologue above overlap that kernel's tail; nothing it wrote is touched before this wait
+    // (a no-op when the launch carries no such attribute).
+    if (FUSE) asm volatile("griddepcontrol.wait;" ::: "memory");
 
     auto issue = [&](int s) {
         const int slot = s % NSTAGE, t = s / nkc, kc = s - t * nkc;
@@ -895,7 +899,13 @@ static int launch_gated_kc(const float* xT, int64_t ld1_total, const float* yT, 
     const size_t smem = gated_smem_bytes<K>(k, KCV, NSTAGE);
     if (K == 1 && prm.tilecnt) {
         F2P_CUDA(cudaFuncSetAttribute(nn_gated_kernel<1, KCV, NSTAGE, 1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        nn_gated_kernel<1, KCV, NSTAGE, 1, 1><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)total_items); cfg.blockDim = dim3(NN_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        F2P_CUDA(cudaLaunchKernelEx(&cfg, nn_gated_kernel<1, KCV, NSTAGE, 1, 1>, mapX, mapY, prm));
     } else if (nxp) {
         F2P_CUDA(cudaFuncSetAttribute(nn_gated_kernel<K, KCV, NSTAGE, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         nn_gated_kernel<K, KCV, NSTAGE, 1><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);

@@ -233,6 +233,9 @@ prep_kernel(const float* __restrict__ ex, const float* __restrict__ Cmat, const 
             float* __restrict__ xT, int64_t ld1_total, float* __restrict__ nx, float* __restrict__ yT, int64_t ld2_total,
             float* __restrict__ ny, int use_ft, u64* __restrict__ best_init, int* __restrict__ tilecnt) {
     extern __shared__ __align__(16) float smem[];
+    // lets a dependent launch (the small-problem arg-min kernel) start its prologue now; it still waits for this whole
+    // grid (griddepcontrol.wait) before reading anything written here
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     if ((int)blockIdx.x < total_xtiles)
         project_body<true>(blockIdx.x, smem, ex, Cmat, pairs, npairs, uni_xtiles, k, xT, ld1_total, nx, use_ft);
     else
