@@ -119,9 +119,10 @@ transpose_body(int bid, float* smem, const float* __restrict__ evecs, const Pair
 template <bool IS_X>
 __global__ void __launch_bounds__(PREP_THREADS)
 transpose_kernel(const float* __restrict__ evecs, const PairDev* __restrict__ pairs, int npairs, int uniform_tiles, int k,
-                 float* __restrict__ outT, int64_t ld_total, float* __restrict__ nrm) {
+                 float* __restrict__ outT, int64_t ld_total, float* __restrict__ nrm, u64* __restrict__ best_init,
+                 int* __restrict__ tilecnt) {
     extern __shared__ __align__(16) float smem[];
-    transpose_body<IS_X>(blockIdx.x, smem, evecs, pairs, npairs, uniform_tiles, k, outT, ld_total, nrm, nullptr, nullptr);
+    transpose_body<IS_X>(blockIdx.x, smem, evecs, pairs, npairs, uniform_tiles, k, outT, ld_total, nrm, best_init, tilecnt);
 }
 
 // Projection: feat = e . C^T for a [TILE][k] tile of points, written k-major as -2*feat, with the fused row norms.
@@ -246,12 +247,13 @@ prep_kernel(const float* __restrict__ ex, const float* __restrict__ Cmat, const 
 // Host launchers -----------------------------------------------------------------------------------
 template <bool IS_X>
 static int launch_project_t(const float* evecs, const float* Cmat, const PairDev* pairs_dev, int npairs, int uniform_tiles,
-                            int total_tiles, int k, float* outT, int64_t ld_total, float* nrm, cudaStream_t stream) {
+                            int total_tiles, int k, float* outT, int64_t ld_total, float* nrm, cudaStream_t stream,
+                            u64* best_init = nullptr, int* tilecnt = nullptr) {
     if (Cmat == nullptr) {
         const size_t smem = (size_t)k * ELD * sizeof(float);
         static bool attr_done = false;
         if (!attr_done) { F2P_CUDA(cudaFuncSetAttribute(transpose_kernel<IS_X>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024)); attr_done = true; }
-        transpose_kernel<IS_X><<<total_tiles, PREP_THREADS, smem, stream>>>(evecs, pairs_dev, npairs, uniform_tiles, k, outT, ld_total, nrm);
+        transpose_kernel<IS_X><<<total_tiles, PREP_THREADS, smem, stream>>>(evecs, pairs_dev, npairs, uniform_tiles, k, outT, ld_total, nrm, best_init, tilecnt);
     } else {
         const size_t base = (size_t)k * (ELD + CLD) * sizeof(float);
         const int use_ft = base + (size_t)k * ELD * sizeof(float) <= 112 * 1024;   // keep 2 CTAs per SM
@@ -264,10 +266,20 @@ static int launch_project_t(const float* evecs, const float* Cmat, const PairDev
     return 0;
 }
 
+constexpr int PREP_FUSE_MAX_TILES = 8 * 148;
+
 int launch_prep(const float* ex, const float* Cmat, const float* ey, const PairDev* pairs_dev, int npairs, int uni_xtiles,
                 int total_xtiles, int uni_ytiles, int total_ytiles, int k, float* xT, int64_t ld1_total, float* nx,
                 float* yT, int64_t ld2_total, float* ny, unsigned long long* best_init, int* tilecnt, cudaStream_t stream) {
     if (total_xtiles + total_ytiles <= 0) return 0;
+    if (total_xtiles + total_ytiles > PREP_FUSE_MAX_TILES) {
+        // big batches: two launches, so the transposing CTAs keep their own (smaller) shared-memory footprint — the
+        // launch boundary is noise there (256 pairs: 0.33 ms as two launches, 0.38 ms as one)
+        int rc = total_xtiles > 0 ? launch_project_t<true>(ex, Cmat, pairs_dev, npairs, uni_xtiles, total_xtiles, k, xT, ld1_total, nx, stream) : 0;
+        if (rc || total_ytiles <= 0) return rc;
+        return launch_project_t<false>(ey, nullptr, pairs_dev, npairs, uni_ytiles, total_ytiles, k, yT, ld2_total, ny, stream,
+                                       reinterpret_cast<u64*>(best_init), tilecnt);
+    }
     const size_t base = (size_t)k * (ELD + CLD) * sizeof(float);
     const int use_ft = base + (size_t)k * ELD * sizeof(float) <= 112 * 1024;   // keep 2 CTAs per SM
     const size_t smem = base + (use_ft ? (size_t)k * ELD * sizeof(float) : 0);

@@ -327,12 +327,14 @@ def run_b200_arm(args, wl):
                 "timer": "host wall clock around synchronized region (includes pinned H2D and result D2H)"},
         "clocks": clocks,
     }
-    # kernels of this library launched per step (projection + transpose with fused norms and arg-min state reset: 1;
-    # naive: gated arg-min with fused finalise 1; spatial: gated top-5 + exact fallback + finalise 3, filter init +
-    # 3 x (vote + classify + verify + combine) 13)
-    # (naive, more than ~8 waves of arg-min items — the large pair, big batches: arg-min + separate finalise, 3 in all)
-    naive_launches = 2 if (n1 * n2 <= 10_000_000 and ppg <= 64) else 3
-    line["gpu_launches"] = (17 if spatial else naive_launches) * args.steps
+    # kernels of this library launched per step.  Preparation (projection + transpose, fused norms, arg-min state reset):
+    # 1 launch up to 8 x 148 tiles, else 2.  Naive: gated arg-min that finalises its own column tiles (1) up to ~8 waves
+    # of items, else arg-min + finalise (2).  Spatial: gated top-5 + exact fallback + finalise 3, filter init +
+    # 3 x (vote + classify + verify + combine) 13.
+    tiles = ppg * ((n1 + 127) // 128 + (n2 + 127) // 128)
+    prep_launches = 1 if tiles <= 8 * 148 else 2
+    naive_launches = 1 if (n1 * n2 <= 10_000_000 and ppg <= 64) else 2
+    line["gpu_launches"] = (prep_launches + (16 if spatial else naive_launches)) * args.steps
 
     if rank == 0 and world == 1 and args.workload == "large" and not args.no_extra:
         line["other_workloads"] = side_workloads()
