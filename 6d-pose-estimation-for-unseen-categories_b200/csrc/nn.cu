@@ -480,9 +480,6 @@ nn_gated_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
         ny2[0] = pack2(n0.x, n0.y); ny2[1] = pack2(n0.z, n0.w);
         ny2[2] = pack2(n1.x, n1.y); ny2[3] = pack2(n1.z, n1.w);
     }
-    float tau[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) tau[j] = INF;
     int kept = 0;                          // threads < TILE: entries their column held after its last cut
 
     mbar_wait(fullB, 0);
@@ -519,7 +516,6 @@ nn_gated_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
             mbar_wait(&full[slot], ph);
             const float* A = sA + (size_t)slot * KC * TILE + ty * 4;
             const float* B = sB + (size_t)kc * KC * TILE + tx * 4;
-            const int klen = min(KC, k - kc * KC);
             auto step = [&](int kk) {
                 const float4 a0 = *reinterpret_cast<const float4*>(A + kk * TILE);
                 const float4 a1 = *reinterpret_cast<const float4*>(A + kk * TILE + 64);
@@ -532,12 +528,12 @@ nn_gated_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
 #pragma unroll
                     for (int i = 0; i < 8; ++i) fma2v(acc[i][j], pack2(av[i], av[i]), bp[j]);
             };
-            if (klen == KC) {
+            // Every stage runs the full unrolled KC steps: the k-rows past k in the last stage are TMA zero fill on BOTH
+            // operands, and fma(0, 0, acc) leaves acc as it is (a -0 accumulator would become +0, which the following
+            // "+ nx" with nx >= +0 maps to the same sum).  The rolled tail loop this replaces ran a third of the
+            // k = 50 work (stages 17 + 17 + 16) at 47 instead of 39 instructions per k-step (ncu, 256 pairs).
 #pragma unroll
-                for (int kk = 0; kk < KC; ++kk) step(kk);
-            } else {
-                for (int kk = 0; kk < klen; ++kk) step(kk);
-            }
+            for (int kk = 0; kk < KC; ++kk) step(kk);
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[slot]);
         }
@@ -547,6 +543,16 @@ nn_gated_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
             nxb = __ldg(reinterpret_cast<const float4*>(prm.nx + xcol + rowbase + 64 + ty * 4));
         }
         const float nxv[8] = {nxa.x, nxa.y, nxa.z, nxa.w, nxb.x, nxb.y, nxb.z, nxb.w};
+        // thresholds of this thread's 8 columns: read from shared memory per tile (K == 5; they only change at a cut) or
+        // per row (K == 1) instead of living in registers across the main loop — at the 128-register cap eight more
+        // live values there cost the top-5 instance one register move per 5 packed FMAs and a spill (ncu, 256 pairs)
+        float tau[8];
+        if (K != 1) {
+            const float4 t0 = *reinterpret_cast<const float4*>(s_tau + tx * 4);
+            const float4 t1 = *reinterpret_cast<const float4*>(s_tau + 64 + tx * 4);
+            tau[0] = t0.x; tau[1] = t0.y; tau[2] = t0.z; tau[3] = t0.w;
+            tau[4] = t1.x; tau[5] = t1.y; tau[6] = t1.z; tau[7] = t1.w;
+        }
         // row i of this thread: values (acc + nx) + ny for its 8 columns, gate against tau, append the rare passes
         auto gate_row = [&](int i) {
             const uint32_t row = (uint32_t)(rowbase + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4)));
