@@ -80,3 +80,32 @@ def solve_sharded(solver: str, C12: Sequence[torch.Tensor], evecs_x: Sequence[to
             if c >= 0:
                 out.append(all_payload[r, i, :, :c].contiguous())
     return out
+
+
+def allgather_packed_maps(flat: torch.Tensor, counts: torch.Tensor, group=None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Returns every rank's spatial maps from the packed form of `spatial_batched(..., packed=True)`.
+
+    flat: int64 [P, W] — pair i's dense [2, M'_i] map is `flat[i, :2*M'_i]`; counts: int32 [P] = M'_i.
+    The result buffer is sized for the worst case (W = 2*5*V2 slots per pair) and mostly unused behind the dense prefix,
+    so the exchange is two steps: the counts first (tiny), then only the first 2*max(M') slots of every
+    pair, as int32 on the wire (indices are < 2^31; row 1 may hold the reference's negative int16 wrap, which int32
+    keeps).  Reading the maximum is the one host sync.  Returns (maps int64 [world, P, 2*Mmax], counts int32 [world, P]):
+    pair i of rank r is `maps[r, i, :2*counts[r, i]].view(2, -1)`.
+    """
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    P = int(flat.shape[0])
+    counts = counts.to(torch.int32).contiguous()
+    all_counts = torch.empty((world * P,), dtype=torch.int32, device=counts.device)
+    if world > 1:
+        dist.all_gather_into_tensor(all_counts, counts, group=group)
+    else:
+        all_counts.copy_(counts)
+    mmax = int(all_counts.max().item()) if all_counts.numel() else 0
+    width = min(2 * mmax, int(flat.shape[1]))
+    wire = flat[:, :width].to(torch.int32).contiguous()
+    all_wire = torch.empty((world * P, width), dtype=torch.int32, device=flat.device)
+    if world > 1 and width > 0:
+        dist.all_gather_into_tensor(all_wire, wire, group=group)
+    else:
+        all_wire.copy_(wire)
+    return all_wire.to(torch.int64).view(world, P, width), all_counts.view(world, P)

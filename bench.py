@@ -227,7 +227,13 @@ def run_b200_arm(args, wl):
         # return the index maps to every rank: NCCL all-gather over NVLink of the rank's result buffer (+ counts)
         if dist is None:
             return
-        parts = list(out[:2]) if spatial else [out]
+        if spatial:
+            # counts first, then only the used prefix of every pair's result slots, int32 on the wire
+            # (fmap2pointmap_solvers.distributed.allgather_packed_maps): the worst-case buffer is 10*n2 int64 slots per
+            # pair and nearly empty behind the dense [2,M'] prefix (8 ranks: 328 MB per rank and step before this)
+            from fmap2pointmap_solvers.distributed import allgather_packed_maps
+            return allgather_packed_maps(out[0], out[1])
+        parts = [out]
         res = []
         for t in parts:
             allm = torch.empty((world,) + tuple(t.shape), dtype=t.dtype, device=dev)

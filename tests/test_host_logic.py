@@ -102,6 +102,50 @@ def _worker(rank, world, port, q):
     dist.destroy_process_group()
 
 
+def _worker_packed(rank, world, port, q):
+    import torch.distributed as dist
+    from fmap2pointmap_solvers.distributed import allgather_packed_maps
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    ok = True
+    try:
+        def rank_data(r):      # what rank r holds: 3 pairs, worst-case width 40, dense [2,M'] prefixes, junk behind them
+            g = torch.Generator().manual_seed(50 + r)
+            counts = torch.tensor([[3, 0, 7], [11, 2, 0]][r], dtype=torch.int32)
+            flat = torch.randint(-40000, 2**31 - 1, (3, 40), generator=g, dtype=torch.int64)
+            return flat, counts
+        flat, counts = rank_data(rank)
+        maps, allc = allgather_packed_maps(flat, counts)
+        ok = ok and tuple(maps.shape) == (2, 3, 22) and maps.dtype == torch.int64 and allc.dtype == torch.int32
+        for r in range(world):
+            f, c = rank_data(r)
+            ok = ok and torch.equal(allc[r], c)
+            for i in range(3):
+                m = int(c[i])
+                ok = ok and torch.equal(maps[r, i, :2 * m].view(2, m), f[i, :2 * m].view(2, m))
+    except Exception:
+        import traceback
+        traceback.print_exc()
+        ok = False
+    q.put((rank, ok))
+    dist.destroy_process_group()
+
+
+def test_packed_map_allgather_gloo_world2():
+    """Counts first, then only the used prefix of every pair's result slots, int32 on the wire."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_worker_packed, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(results) == [(0, True), (1, True)]
+
+
 def test_pair_sharding_allgather_gloo_world2():
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
