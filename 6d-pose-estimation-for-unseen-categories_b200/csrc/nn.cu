@@ -880,10 +880,10 @@ static size_t gated_smem_bytes(int k, int kc, int nstage) {
 // zero-fill on both operands (fma(0, 0, acc) == acc: acc is never -0).  F2P_GATED_KC overrides (tools/nn_time.py).
 static int choose_gated_kc(int k) {
     static const int forced = [] { const char* e = getenv("F2P_GATED_KC"); return e ? atoi(e) : 0; }();
-    if (forced == 15 || forced == 16 || forced == 17) return forced;
+    if (forced == 15 || forced == 16 || forced == 17 || forced == 25) return forced;
     int best = 16, best_pad = 1 << 30, best_n = 1 << 30;
-    const int cand[3] = {16, 17, 15};
-    for (int c = 0; c < 3; ++c) {
+    const int cand[4] = {16, 17, 15, 25};   // 25: k = 50 as 2 full stages (no padded step, one barrier round trip fewer per tile)
+    for (int c = 0; c < (k <= 50 ? 4 : 3); ++c) {   // 25-row stages only where two top-5 CTAs still fit one SM's shared memory
         const int n = (k + cand[c] - 1) / cand[c], pad = n * cand[c] - k;
         if (pad < best_pad || (pad == best_pad && n < best_n)) { best = cand[c]; best_pad = pad; best_n = n; }
     }
@@ -929,6 +929,7 @@ static int launch_gated(const float* xT, int64_t ld1_total, const float* yT, int
     switch (choose_gated_kc(k)) {
         case 15: return launch_gated_kc<K, 15>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
         case 17: return launch_gated_kc<K, 17>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
+        case 25: return launch_gated_kc<K, 25>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
         default: return launch_gated_kc<K, 16>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
     }
 }
