@@ -162,3 +162,17 @@ def test_cfg3_full_batch_4096_pairs_naive_and_batch_invariance(solvers, oracle, 
     for i, r in enumerate(sl):
         m = int(ch[a + i])
         assert r.shape[1] == m and torch.equal(r, flat[a + i, :2 * m].view(2, m))
+
+
+# ---------------------------------------------------------------------------------------------- stage lengths
+@pytest.mark.parametrize("k", [7, 18, 31, 33, 37, 41, 49, 50, 51, 66, 99, 127, 130])
+def test_every_stage_length_and_padded_last_stage(solvers, oracle, k):
+    """Kernel 2 picks 15 / 16 / 17 / 25 k-rows per TMA stage and always runs whole stages: the rows past k in the last
+    stage are TMA zero fill.  Basis sizes around every stage boundary, both solvers, several row tiles, bit-exact."""
+    from fmap2pointmap_solvers.synth import make_pair
+    p = make_pair(1100, 390, k, seed=7000 + k)
+    C, ex, ey, cad, pc = (t.cuda() for t in (p.C12, p.evecs_x, p.evecs_y, p.CAD, p.PC))
+    got = solvers.naive_fmap2pointmap(C, ex, ey).cpu().numpy()
+    np.testing.assert_array_equal(got, oracle.naive(p.C12, p.evecs_x, p.evecs_y, int16_compat=False))
+    got = solvers.spacial_filtering_fmap2pointmap(C, ex, ey, CAD=cad, PC=pc, diam_cad=p.diam_cad * 2.5).cpu().numpy()
+    np.testing.assert_array_equal(got, oracle.spatial(p.C12, p.evecs_x, p.evecs_y, p.CAD, p.PC, p.diam_cad * 2.5))
