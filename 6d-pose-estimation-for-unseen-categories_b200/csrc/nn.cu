@@ -880,17 +880,20 @@ static size_t gated_smem_bytes(int k, int kc, int nstage) {
 // zero-fill on both operands (fma(0, 0, acc) == acc: acc is never -0).  F2P_GATED_KC overrides (tools/nn_time.py).
 static int choose_gated_kc(int k) {
     static const int forced = [] { const char* e = getenv("F2P_GATED_KC"); return e ? atoi(e) : 0; }();
-    if (forced == 15 || forced == 16 || forced == 17 || forced == 25) return forced;
+    if (forced == 15 || forced == 16 || forced == 17 || forced == 25 || (forced == 50 && k <= 50)) return forced;
     int best = 16, best_pad = 1 << 30, best_n = 1 << 30;
-    const int cand[4] = {16, 17, 15, 25};   // 25: k = 50 as 2 full stages (no padded step, one barrier round trip fewer per tile)
-    for (int c = 0; c < (k <= 50 ? 4 : 3); ++c) {   // 25-row stages only where two top-5 CTAs still fit one SM's shared memory
+    // 25 / 50 (k <= 50 only, where two top-5 CTAs still fit one SM's shared memory): k = 50 runs as ONE 50-row stage per
+    // tile on a 2-deep ring (same shared memory as 4 x 12.5-row-equivalents): no padded step, one barrier round trip per
+    // tile.  Measured per 256 pairs, top-5: 3 x 17 6.21 ms, 2 x 25 5.98 ms, 1 x 50 5.92 ms.
+    const int cand[5] = {16, 17, 15, 25, 50};
+    for (int c = 0; c < (k <= 50 ? 5 : 3); ++c) {
         const int n = (k + cand[c] - 1) / cand[c], pad = n * cand[c] - k;
         if (pad < best_pad || (pad == best_pad && n < best_n)) { best = cand[c]; best_pad = pad; best_n = n; }
     }
     return best;
 }
 
-template <int K, int KCV>
+template <int K, int KCV, int NST = NSTAGE>
 static int launch_gated_kc(const float* xT, int64_t ld1_total, const float* yT, int64_t ld2_total, int k, const NNParams& prm,
                            int total_items, cudaStream_t stream) {
     CUtensorMap mapX, mapY;
@@ -902,22 +905,22 @@ static int launch_gated_kc(const float* xT, int64_t ld1_total, const float* yT, 
     // F2P_GATED_NXP overrides (tools/nn_time.py).
     const char* ep = getenv("F2P_GATED_NXP");
     const int nxp = ep ? atoi(ep) : (K == 1 ? 1 : 0);
-    const size_t smem = gated_smem_bytes<K>(k, KCV, NSTAGE);
+    const size_t smem = gated_smem_bytes<K>(k, KCV, NST);
     if (K == 1 && prm.tilecnt) {
-        F2P_CUDA(cudaFuncSetAttribute(nn_gated_kernel<1, KCV, NSTAGE, 1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        F2P_CUDA(cudaFuncSetAttribute(nn_gated_kernel<1, KCV, NST, 1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned)total_items); cfg.blockDim = dim3(NN_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         at[0].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = at; cfg.numAttrs = 1;
-        F2P_CUDA(cudaLaunchKernelEx(&cfg, nn_gated_kernel<1, KCV, NSTAGE, 1, 1>, mapX, mapY, prm));
+        F2P_CUDA(cudaLaunchKernelEx(&cfg, nn_gated_kernel<1, KCV, NST, 1, 1>, mapX, mapY, prm));
     } else if (nxp) {
-        F2P_CUDA(cudaFuncSetAttribute(nn_gated_kernel<K, KCV, NSTAGE, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        nn_gated_kernel<K, KCV, NSTAGE, 1><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);
+        F2P_CUDA(cudaFuncSetAttribute(nn_gated_kernel<K, KCV, NST, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        nn_gated_kernel<K, KCV, NST, 1><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);
     } else {
-        F2P_CUDA(cudaFuncSetAttribute(nn_gated_kernel<K, KCV, NSTAGE, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        nn_gated_kernel<K, KCV, NSTAGE, 0><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);
+        F2P_CUDA(cudaFuncSetAttribute(nn_gated_kernel<K, KCV, NST, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        nn_gated_kernel<K, KCV, NST, 0><<<total_items, NN_THREADS, smem, stream>>>(mapX, mapY, prm);
     }
     F2P_CUDA(cudaGetLastError());
     return 0;
@@ -930,6 +933,7 @@ static int launch_gated(const float* xT, int64_t ld1_total, const float* yT, int
         case 15: return launch_gated_kc<K, 15>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
         case 17: return launch_gated_kc<K, 17>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
         case 25: return launch_gated_kc<K, 25>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
+        case 50: return launch_gated_kc<K, 50, 2>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
         default: return launch_gated_kc<K, 16>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
     }
 }
