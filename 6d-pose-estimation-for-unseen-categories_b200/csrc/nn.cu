@@ -878,17 +878,20 @@ static size_t gated_smem_bytes(int k, int kc, int nstage) {
 // stage is full and runs the unrolled loop — k = 50 -> 3 x 17 instead of 3 x 16 + a 2-step tail stage that costs a
 // whole barrier round trip and a rolled loop; k = 30 -> 2 x 15; k = 64 / 128 -> 16.  The padded k-rows are TMA
 // zero-fill on both operands (fma(0, 0, acc) == acc: acc is never -0).  F2P_GATED_KC overrides (tools/nn_time.py).
-static int choose_gated_kc(int k) {
+static int choose_gated_kc(int k, int total_items) {
     static const int forced = [] { const char* e = getenv("F2P_GATED_KC"); return e ? atoi(e) : 0; }();
     if (forced == 15 || forced == 16 || forced == 17 || forced == 25 || (forced == 50 && k <= 50) || forced == 32) return forced;
     int best = 16, best_pad = 1 << 30, best_n = 1 << 30;
     // 25 / 50 (k <= 50 only, where two top-5 CTAs still fit one SM's shared memory): k = 50 runs as ONE 50-row stage per
     // tile on a 2-deep ring (same shared memory as 4 x 12.5-row-equivalents): no padded step, one barrier round trip per
     // tile.  Measured per 256 pairs, top-5: 3 x 17 6.21 ms, 2 x 25 5.98 ms, 1 x 50 5.92 ms.
-    // 32 (k > 50): 32-row stages on a 2-deep ring, the shared memory of 16-row stages on the 4-deep ring — k = 128 runs 4
-    // barrier round trips per tile instead of 8: 100k x 100k x 128 arg-min 44.40 -> 43.89 ms.
+    // 32: 32-row stages on a 2-deep ring, the shared memory of 16-row stages on the 4-deep ring — k = 128 runs 4 barrier
+    // round trips per tile instead of 8.  Measured: 100k x 100k x 128 (12.5k work items) 44.40 -> 43.89 ms, but
+    // 50k x 20k x 128 (3.8k items) 4.79 -> 5.00 ms and 50k x 20k x 64 3.01 -> 3.46 ms, so it is taken for k >= 128 and
+    // long grids only (tools/kc32.sh, tools/kc64.sh).
+    const bool deep = k >= 128 && total_items >= 8192;
     const int cand[5] = {16, 17, 15, k <= 50 ? 25 : 32, 50};
-    for (int c = 0; c < (k <= 50 ? 5 : 4); ++c) {
+    for (int c = 0; c < (k <= 50 ? 5 : (deep ? 4 : 3)); ++c) {
         const int n = (k + cand[c] - 1) / cand[c], pad = n * cand[c] - k;
         if (pad < best_pad || (pad == best_pad && n < best_n)) { best = cand[c]; best_pad = pad; best_n = n; }
     }
@@ -931,7 +934,7 @@ static int launch_gated_kc(const float* xT, int64_t ld1_total, const float* yT, 
 template <int K>
 static int launch_gated(const float* xT, int64_t ld1_total, const float* yT, int64_t ld2_total, int k, const NNParams& prm,
                         int total_items, cudaStream_t stream) {
-    switch (choose_gated_kc(k)) {
+    switch (choose_gated_kc(k, total_items)) {
         case 15: return launch_gated_kc<K, 15>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
         case 17: return launch_gated_kc<K, 17>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
         case 25: return launch_gated_kc<K, 25>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);
