@@ -42,7 +42,7 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 int make_tensor_map_2d(CUtensorMap* map, const float* base, uint64_t cols, uint64_t rows, uint64_t row_stride_elems,
-                       uint32_t box_cols, uint32_t box_rows) {
+                       uint32_t box_cols, uint32_t box_rows, int swizzle128) {
     EncodeTiledFn fn = get_encode_fn();
     if (!fn) { set_error("cuTensorMapEncodeTiled entry point unavailable"); return F2P_EDEVICE; }
     cuuint64_t dims[2] = {cols, rows};
@@ -50,7 +50,8 @@ int make_tensor_map_2d(CUtensorMap* map, const float* base, uint64_t cols, uint6
     cuuint32_t box[2] = {box_cols, box_rows};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (%d) cols=%llu rows=%llu", (int)r,
                                        (unsigned long long)cols, (unsigned long long)rows); return F2P_EDEVICE; }
@@ -106,8 +107,12 @@ struct Plan {
     double flops = 0;                                    // 2*n1*n2*k summed over pairs
     // workspace offsets (bytes)
     size_t off_pairs = 0, off_fpairs = 0, off_xT = 0, off_nx = 0, off_yT = 0, off_ny = 0, off_keys = 0, off_cand = 0,
-           off_filter = 0, total_bytes = 0;
+           off_filter = 0, off_tc = 0, total_bytes = 0;
     std::vector<size_t> filter_off;
+    // tensor-pipe screen (tc.cu)
+    bool use_tc = false;
+    int spatial = 0;
+    TCPlan tc;
 };
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -149,6 +154,24 @@ static int build_plan(const F2PPairDesc* d, int npairs, int k, int spatial, bool
         if (5 * p.n2 > P.maxM) P.maxM = 5 * p.n2;
         P.flops += 2.0 * p.n1 * (double)p.n2 * k;
     }
+    // tensor-pipe screen: its own row tiling (256-row tiles, one CTA per SM)
+    P.spatial = spatial;
+    P.use_tc = npairs > 0 && tc_enabled(P.flops, k);
+    P.tc = TCPlan();
+    if (P.use_tc) {
+        int64_t rows = 0, items = 0, xt = 0;
+        for (int i = 0; i < npairs; ++i) {
+            PairDev& p = P.pairs[i];
+            p.tc_nrt = (p.n1 + TC_ROWS - 1) / TC_ROWS;
+            p.tc_nsplit = choose_tc_nsplit(base_items, p.tc_nrt, sm_count());
+            if (rows + (int64_t)p.tc_nrt * TC_ROWS > 0x7fffff00ll || items + (int64_t)p.nct * p.tc_nsplit > 0x7fffff00ll) {
+                set_error("batch too large for 32-bit tile indexing; split the batch"); return F2P_ENOTSUP;
+            }
+            p.xa_row0 = (int)rows; p.tc_item0 = (int)items; p.tc_xtile0 = (int)xt;
+            rows += (int64_t)p.tc_nrt * TC_ROWS; items += (int64_t)p.nct * p.tc_nsplit; xt += 2 * p.tc_nrt;
+        }
+        P.tc.ld1_tc_total = rows; P.tc.total_items = (int)items; P.tc.total_xtiles = (int)xt;
+    }
     auto uniform = [&](auto getter) {
         if (npairs == 0) return 0;
         const int v = getter(P.pairs[0]);
@@ -158,6 +181,10 @@ static int build_plan(const F2PPairDesc* d, int npairs, int k, int spatial, bool
     P.uni_xtiles = uniform([](const PairDev& p) { return p.nrt; });
     P.uni_ytiles = uniform([](const PairDev& p) { return p.nct; });
     P.uni_items = uniform([](const PairDev& p) { return p.nct * p.nsplit; });
+    if (P.use_tc) {
+        P.tc.uni_items = uniform([](const PairDev& p) { return p.nct * p.tc_nsplit; });
+        P.tc.uni_xtiles = uniform([](const PairDev& p) { return 2 * p.tc_nrt; });
+    }
 
     size_t o = 0;
     P.off_pairs = o; o = align_up(o + sizeof(PairDev) * (size_t)(npairs > 0 ? npairs : 1), 256);
@@ -175,8 +202,19 @@ static int build_plan(const F2PPairDesc* d, int npairs, int k, int spatial, bool
         P.filter_off.resize(npairs);
         for (int i = 0; i < npairs; ++i) { P.filter_off[i] = o; o += filter_pair_bytes(5 * P.pairs[i].n2); }
     }
+    if (P.use_tc) {
+        P.off_tc = o;
+        o = align_up(o + tc_ws_bytes(P.tc.ld1_tc_total, P.ld2_total, k, P.tc.total_items, P.total_ytiles, npairs, spatial), 256);
+    }
     P.total_bytes = o;
     return 0;
+}
+
+// carves the tensor-pipe workspace of a call; returns the plan to hand to launch_argmin / launch_top5 (or null)
+static const TCPlan* tc_plan(Plan& P, unsigned char* ws, int k, int npairs) {
+    if (!P.use_tc) return nullptr;
+    tc_ws_carve(P.tc.ws, ws + P.off_tc, P.tc.ld1_tc_total, P.ld2_total, k, P.tc.total_items, P.total_ytiles, npairs, P.spatial);
+    return &P.tc;
 }
 
 static int check_ws(const Plan& P, void* ws, size_t ws_bytes) {
@@ -244,7 +282,8 @@ int f2p_naive_batched(const float* ex, const float* ey, const float* C, const F2
     const PairDev* pd = reinterpret_cast<const PairDev*>(ws + P.off_pairs);
     rc = launch_argmin(reinterpret_cast<float*>(ws + P.off_xT), P.ld1_total, reinterpret_cast<float*>(ws + P.off_nx),
                          reinterpret_cast<float*>(ws + P.off_yT), P.ld2_total, reinterpret_cast<float*>(ws + P.off_ny), k, pd,
-                         npairs, P.uni_items, P.total_items, P.uni_ytiles, P.total_ytiles, P.flops, flags, out, aw, st, true);
+                         npairs, P.uni_items, P.total_items, P.uni_ytiles, P.total_ytiles, P.flops, flags, out, aw, st, true,
+                         tc_plan(P, ws, k, npairs));
     stage_mark(2, st);
     return rc;
 }
@@ -272,7 +311,7 @@ int f2p_spatial_batched(const float* ex, const float* ey, const float* C, const 
     rc = launch_top5(reinterpret_cast<float*>(ws + P.off_xT), P.ld1_total, reinterpret_cast<float*>(ws + P.off_nx),
                      reinterpret_cast<float*>(ws + P.off_yT), P.ld2_total, reinterpret_cast<float*>(ws + P.off_ny), k, pd,
                      npairs, P.uni_items, P.total_items, P.uni_ytiles, P.total_ytiles, flags, part5, cand,
-                     cand_dev != nullptr, st);
+                     cand_dev != nullptr, st, tc_plan(P, ws, k, npairs));
     if (rc) return rc;
     stage_mark(2, st);
     return run_filter_batch(P.pairs.data(), npairs, cad, pc, cand, cand_dev != nullptr, out, counts, status,

@@ -22,10 +22,24 @@ int single_pair(PairDev& p, int n1, int n2, int ld1, int ld2, int nsplit_hint) {
     return 0;
 }
 
-int pick_nsplit(int nrt, int nct) {
+int sm_count_now() {
     int dev = 0, sm = 148;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev);
-    return choose_nsplit(nct, nrt, sm);
+    return sm > 0 ? sm : 148;
+}
+
+int pick_nsplit(int nrt, int nct) { return choose_nsplit(nct, nrt, sm_count_now()); }
+
+// tensor-pipe screen geometry of a single pair (tc.cu); returns false when the screen is not used for this shape
+bool single_pair_tc(PairDev& p, int k, TCPlan& tc) {
+    if (!tc_enabled(2.0 * p.n1 * (double)p.n2 * k, k)) return false;
+    p.tc_nrt = (p.n1 + TC_ROWS - 1) / TC_ROWS;
+    p.tc_nsplit = choose_tc_nsplit(p.nct, p.tc_nrt, sm_count_now());
+    p.tc_item0 = 0; p.tc_xtile0 = 0; p.xa_row0 = 0;
+    tc.total_items = tc.uni_items = p.nct * p.tc_nsplit;
+    tc.total_xtiles = tc.uni_xtiles = 2 * p.tc_nrt;
+    tc.ld1_tc_total = (int64_t)p.tc_nrt * TC_ROWS;
+    return true;
 }
 
 }  // namespace
@@ -56,6 +70,12 @@ size_t f2p_nn_workspace_bytes(int n1, int n2, int k, int top5) {
     size_t b = 256;
     if (top5) b += top5_ws_bytes((int64_t)nct * ns, nct);
     else b += argmin_ws_bytes((int64_t)nct * TILE, k, 1);
+    b = (b + 255) & ~(size_t)255;
+    PairDev p; memset(&p, 0, sizeof(p));
+    p.n1 = n1; p.n2 = n2; p.nct = nct;
+    TCPlan tc;
+    if (n1 >= 1 && n2 >= 1 && single_pair_tc(p, k, tc))
+        b += tc_ws_bytes(tc.ld1_tc_total, (int64_t)nct * TILE, k, tc.total_items, nct, 1, top5);
     return (b + 255) & ~(size_t)255;
 }
 
@@ -77,17 +97,24 @@ static int nn_common(int mode, const float* xT, const float* nx, int n1, int ld1
     }
     unsigned char* ws = static_cast<unsigned char*>(ws_v);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int items = p.nct * p.nsplit;
+    TCPlan tc;
+    const bool use_tc = ld2 == nct * TILE && single_pair_tc(p, k, tc);
+    if (use_tc) {
+        size_t off = 256 + (mode ? top5_ws_bytes(items, p.nct) : argmin_ws_bytes(ld2, k, 1));
+        off = (off + 255) & ~(size_t)255;
+        tc_ws_carve(tc.ws, ws + off, tc.ld1_tc_total, ld2, k, tc.total_items, p.nct, 1, mode);
+    }
     F2P_CUDA(cudaMemcpyAsync(ws, &p, sizeof(p), cudaMemcpyHostToDevice, st));
     const PairDev* pd = reinterpret_cast<const PairDev*>(ws);
-    const int items = p.nct * p.nsplit;
     if (mode == 0) {
         ArgminWs aw;
         argmin_ws_carve(aw, ws + 256, ld2, k, 1);
         return launch_argmin(xT, ld1, nx, yT, ld2, ny, k, pd, 1, items, items, p.nct, p.nct, 2.0 * n1 * (double)n2 * k,
-                             F2P_ROW0_ONLY, out, aw, st);
+                             F2P_ROW0_ONLY, out, aw, st, false, use_tc ? &tc : nullptr);
     }
     return launch_top5(xT, ld1, nx, yT, ld2, ny, k, pd, 1, items, items, p.nct, p.nct, F2P_ROW0_ONLY,
-                       reinterpret_cast<unsigned long long*>(ws + 256), out, 1, st);
+                       reinterpret_cast<unsigned long long*>(ws + 256), out, 1, st, use_tc ? &tc : nullptr);
 }
 
 int f2p_nn_argmin(const float* xT, const float* nx, int n1, int ld1, const float* yT, const float* ny, int n2, int ld2,
@@ -109,6 +136,13 @@ int f2p_spatial_filter(const float* cad, int ncad, const float* pc, int npc, con
     if (M > 524288) { set_error("M > 524288 candidates unsupported"); return F2P_ENOTSUP; }
     return run_filter_single(cad, ncad, pc, npc, p, M, thr, out, count, status, mask, scores,
                              static_cast<unsigned char*>(ws), ws_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int f2p_measure_tf32_peak(double* tflops, void* stream) { return measure_tf32_peak(tflops, static_cast<cudaStream_t>(stream)); }
+
+int f2p_tc_last_stats(unsigned long long out[8]) {
+    if (!out) { set_error("null pointer"); return F2P_EINVAL; }
+    return tc_last_stats(out);
 }
 
 int f2p_measure_fp32_peak(double* packed, double* scalar, void* stream) {

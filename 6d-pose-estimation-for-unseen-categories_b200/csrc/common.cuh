@@ -31,6 +31,12 @@ struct PairDev {
     int xtile0, ytile0;      // prefix sums of nrt / nct (prep-kernel work items)
     int cand0;               // first candidate slot of this pair (prefix sum of 5*n2), spatial only
     float thr[4];
+    // tensor-pipe screen (tc.cu): CAD rows re-packed K-major in 256-row tiles
+    int tc_nrt;              // 256-row tiles over n1
+    int tc_nsplit;           // row splits per column tile
+    int tc_item0;            // first screen work item of this pair (prefix sum of nct*tc_nsplit)
+    int tc_xtile0;           // prefix sum of 2*tc_nrt (128-row packing tiles)
+    int xa_row0;             // first row of this pair in the packed XA operand (multiple of 256)
 };
 
 // thread-local error text (f2p_last_error)
@@ -132,7 +138,8 @@ __device__ __forceinline__ int find_pair(int item, const PairDev* __restrict__ p
 #endif  // __CUDACC__
 
 // Host-side: encode a 2-D FP32 tensor map {inner = cols, outer = rows} with box {box_cols, box_rows}.
+// swizzle128 != 0: CU_TENSOR_MAP_SWIZZLE_128B (box_cols * 4 must be 128), the layout tcgen05 descriptors expect.
 int make_tensor_map_2d(CUtensorMap* map, const float* base, uint64_t cols, uint64_t rows, uint64_t row_stride_elems,
-                       uint32_t box_cols, uint32_t box_rows);
+                       uint32_t box_cols, uint32_t box_rows, int swizzle128 = 0);
 
 }  // namespace f2p

@@ -41,6 +41,7 @@ static inline int choose_nsplit(long long base_items, int nrt, int sm, int min_t
     return (int)ns_big;
 }
 
+struct TCPlan;
 // prep.cu
 int launch_project(bool is_x, const float* evecs, const float* Cmat, const PairDev* pairs_dev, int npairs,
                    int uniform_tiles, int total_tiles, int k, float* outT, int64_t ld_total, float* nrm,
@@ -62,11 +63,58 @@ void argmin_ws_carve(ArgminWs& w, unsigned char* base, int64_t ld2_total, int k,
 int launch_argmin(const float* xT, int64_t ld1_total, const float* nx, const float* yT, int64_t ld2_total,
                   const float* ny, int k, const PairDev* pairs_dev, int npairs, int uniform_items, int total_items,
                   int uniform_ytiles, int total_ytiles, double flops, unsigned flags, int64_t* out, const ArgminWs& w,
-                  cudaStream_t stream, bool pre_init = false);
+                  cudaStream_t stream, bool pre_init = false, const TCPlan* tc = nullptr);
 int launch_top5(const float* xT, int64_t ld1_total, const float* nx, const float* yT, int64_t ld2_total, const float* ny,
                 int k, const PairDev* pairs_dev, int npairs, int uniform_items, int total_items, int uniform_ytiles,
                 int total_ytiles, unsigned flags, unsigned long long* part5, int64_t* cand, int cand_is_out_layout,
-                cudaStream_t stream);
+                cudaStream_t stream, const TCPlan* tc = nullptr);
+// tc.cu — tensor-pipe (tcgen05, TF32) screen + exact verification of kernel 2
+constexpr int TC_ROWS = 256;   // CAD rows per accumulator tile of the screen
+constexpr int TC_EH = 2;       // epilogue threads per scene point (4 * TC_EH epilogue warps)
+struct TCWs {
+    float* XA; float* YA; uint32_t* tau; unsigned long long* cand; int* ccnt;
+    unsigned char* zero_base; size_t zero_bytes;      // stats | nxmax | tcflag | pair_bad, cleared per call
+    unsigned long long* stats; uint32_t* nxmax; int* tcflag; int* pair_bad;
+};
+// what the batch plan hands to launch_argmin / launch_top5 when the tensor-pipe screen is used (null = FFMA2 only)
+struct TCPlan {
+    int uni_items, total_items;       // screen work items (column tile x row split)
+    int uni_xtiles, total_xtiles;     // 128-row packing tiles of the XA operand
+    int64_t ld1_tc_total;             // rows of XA (every pair padded to a multiple of TC_ROWS)
+    TCWs ws;
+};
+int tc_kp(int k);
+size_t tc_ws_bytes(int64_t ld1_tc_total, int64_t ld2_total, int k, int64_t tc_items, int64_t total_ytiles, int npairs, int top5);
+void tc_ws_carve(TCWs& w, unsigned char* base, int64_t ld1_tc_total, int64_t ld2_total, int k, int64_t tc_items,
+                 int64_t total_ytiles, int npairs, int top5);
+int launch_tc(int top5, const float* xT, int64_t ld1_total, const float* nx, const float* yT, int64_t ld2_total,
+              const float* ny, int k, const PairDev* pairs_dev, int npairs, int uniform_tc_items, int total_tc_items,
+              int uniform_tc_xtiles, int total_tc_xtiles, int uniform_ytiles, int total_ytiles, int64_t ld1_tc_total,
+              unsigned flags, unsigned long long* best, int64_t* out5, int cand_is_out_layout, const TCWs& w,
+              cudaStream_t stream);
+// Row splits per column tile of the screen (one CTA per SM, each owning all of TMEM): whole waves on `sm` SMs, every
+// item streaming >= 8 tiles of 256 rows when the problem allows (per-CTA fixed cost ~ 2.5 tile times: TMEM allocation,
+// barrier init, the resident scene tile, pipeline fill and drain).
+static inline int choose_tc_nsplit(long long base_items, int nrt, int sm) {
+    if (base_items <= 0 || nrt <= 1) return 1;
+    long long cap = nrt / 8 > 0 ? nrt / 8 : 1;
+    if (base_items * cap < sm) cap = nrt / 2 > 0 ? nrt / 2 : 1;      // tiny problems: fill the SMs first
+    long long best = 1;
+    double best_cost = 1e300;
+    for (long long ns = 1; ns <= cap && ns <= 64; ++ns) {
+        const long long waves = (base_items * ns + sm - 1) / sm;
+        const double cost = (double)waves * (2.5 + (double)((nrt + ns - 1) / ns));
+        if (cost < best_cost * (1.0 - 1e-9)) { best_cost = cost; best = ns; }
+    }
+    return (int)best;
+}
+// Tensor-pipe path selection (F2P_NN_PATH=tc forces it, =gated / exact / two_phase disable it): by default problems with
+// at least TC_MIN_FLOPS of distance work whose k fills a 128-byte swizzle row.  Non-semantic: every path is exact.
+constexpr double TC_MIN_FLOPS = 4.0e10;
+bool tc_enabled(double flops, int k);
+int measure_tf32_peak(double* tflops, cudaStream_t st);
+int tc_last_stats(unsigned long long out[8]);
+
 // filter.cu
 size_t filter_pair_bytes(int M);
 size_t filter_table_bytes(int npairs);

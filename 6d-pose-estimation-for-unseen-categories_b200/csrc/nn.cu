@@ -29,7 +29,10 @@ struct NNParams {
     u64* best;           // MODE 0/2: [ld2_total] packed (value bits << 32 | i) keys, pre-set to ~0
     u64* part5;          // MODE 1: [total_items][TILE][5] keys
     uint32_t* best2;     // MODE 2: [ld2_total] bits of the second-smallest clamped d2 per column, pre-set to +inf bits
-    const int* ncols;    // MODE 0 re-check pass: per-pair number of (compacted) columns to process, or null = n2
+    const int* ncols;    // MODE 0 re-check pass: per-pair number of (compacted) columns to process, or null = n2.
+                         // Gated kernels behind the tensor-pipe screen (tc.cu) read it as [total column tiles] flags and
+                         // process only the tiles the screen flagged (null = everything) — the struct keeps its size, the
+                         // gated kernels' register allocation at the 128-register cap is sensitive to it
     int* tileflag;       // [total column tiles]: gated kernel sets 1 when a candidate list overflowed; MODE 0/1 launched
                          // as the exact fallback process only flagged column tiles (null = process everything)
     int* tilecnt;        // gated arg-min, fused finalise: [total column tiles] arrival counters (pre-set to 0), or null
@@ -443,6 +446,7 @@ nn_gated_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
     const int xcol = pdp->x_col0, ycol = pdp->y_col0 + ct * TILE;
     const int total_stages = ntiles * nkc;
     const float INF = __int_as_float(0x7f800000);
+    if (prm.ncols && prm.ncols[pdp->ytile0 + ct] == 0) return;   // decided by the tensor-pipe screen (uniform exit)
 
     if (tid == 0) {
         tma_prefetch_desc(&mapX);
@@ -741,7 +745,8 @@ finalize_argmin_kernel(const u64* __restrict__ best, const PairDev* __restrict__
 // (spacial_filtering.py:36-38): column 5j+r = (r-th nearest CAD row of scene point j, j).
 __global__ void __launch_bounds__(TILE)
 finalize_top5_kernel(const u64* __restrict__ part5, const PairDev* __restrict__ pairs, int npairs, int uniform_tiles,
-                     unsigned flags, int64_t* __restrict__ cand, int cand_is_out_layout) {
+                     unsigned flags, int64_t* __restrict__ cand, int cand_is_out_layout, const int* __restrict__ tc_only) {
+    if (tc_only && tc_only[blockIdx.x] == 0) return;   // this tile's candidates were written by the tensor-pipe path
     const int pi = find_pair(blockIdx.x, pairs, npairs, uniform_tiles, &PairDev::ytile0);
     const PairDev* pd = pairs + pi;
     const int ct = blockIdx.x - pd->ytile0;
@@ -977,8 +982,17 @@ enum NNPath { PATH_GATED = 0, PATH_EXACT = 1, PATH_TWO_PHASE = 2 };
 static NNPath nn_path() {
     const char* e = getenv("F2P_NN_PATH");
     if (e && e[0] == 'e') return PATH_EXACT;
-    if (e && e[0] == 't') return PATH_TWO_PHASE;
+    if (e && e[0] == 't' && e[1] == 'w') return PATH_TWO_PHASE;
     return PATH_GATED;
+}
+// "tc": tensor-pipe screen in front of the gated kernels regardless of size; "gated" / "exact" / "two_phase": never;
+// unset: by size.  Every choice gives the same (exact) result.
+bool tc_enabled(double flops, int k) {
+    if (tc_kp(k) < 32) return false;          // the packed rows must fill one 128-byte swizzle row
+    const char* e = getenv("F2P_NN_PATH");
+    if (e && e[0] == 't' && e[1] == 'c') return true;
+    if (e && e[0]) return false;
+    return flops >= TC_MIN_FLOPS;
 }
 
 constexpr int FUSE_MAX_ITEMS = 16 * 148;   // ~8 waves of 2 CTAs per SM on a B200
@@ -986,7 +1000,7 @@ constexpr int FUSE_MAX_ITEMS = 16 * 148;   // ~8 waves of 2 CTAs per SM on a B20
 int launch_argmin(const float* xT, int64_t ld1_total, const float* nx, const float* yT, int64_t ld2_total,
                   const float* ny, int k, const PairDev* pairs_dev, int npairs, int uniform_items, int total_items,
                   int uniform_ytiles, int total_ytiles, double flops, unsigned flags, int64_t* out, const ArgminWs& w,
-                  cudaStream_t stream, bool pre_init) {
+                  cudaStream_t stream, bool pre_init, const TCPlan* tc) {
     if (total_items <= 0 || total_ytiles <= 0) return 0;
     NNParams prm;
     prm.pairs = pairs_dev; prm.npairs = npairs; prm.uniform_items = uniform_items; prm.k = k;
@@ -996,6 +1010,20 @@ int launch_argmin(const float* xT, int64_t ld1_total, const float* nx, const flo
     (void)flops;
     const unsigned iblocks = (unsigned)((ld2_total + 255) / 256);
     int rc;
+    if (tc) {
+        // tensor-pipe screen + exact verification merge their keys into `best`; the gated kernel then only runs the
+        // column tiles the screen flagged (its CTAs exit at once everywhere else)
+        if (!pre_init)
+            argmin_init_kernel<<<iblocks, 256, 0, stream>>>(w.best, nullptr, nullptr, (size_t)ld2_total, nullptr, 0, nullptr);
+        if ((rc = launch_tc(0, xT, ld1_total, nx, yT, ld2_total, ny, k, pairs_dev, npairs, tc->uni_items, tc->total_items,
+                            tc->uni_xtiles, tc->total_xtiles, uniform_ytiles, total_ytiles, tc->ld1_tc_total, flags, w.best,
+                            nullptr, 0, tc->ws, stream))) return rc;
+        prm.ncols = tc->ws.tcflag;
+        if ((rc = launch_gated<1>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream))) return rc;
+        finalize_argmin_kernel<<<total_ytiles, TILE, 0, stream>>>(w.best, pairs_dev, npairs, uniform_ytiles, flags, out);
+        F2P_CUDA(cudaGetLastError());
+        return 0;
+    }
     if (path == PATH_GATED && pre_init && total_items <= FUSE_MAX_ITEMS) {
         // small problem (a few waves): keys and arrival counters were reset by launch_prep, the kernel finalises its own
         // column tiles — one launch instead of three
@@ -1035,22 +1063,34 @@ int launch_argmin(const float* xT, int64_t ld1_total, const float* nx, const flo
 
 int launch_top5(const float* xT, int64_t ld1_total, const float* nx, const float* yT, int64_t ld2_total, const float* ny,
                 int k, const PairDev* pairs_dev, int npairs, int uniform_items, int total_items, int uniform_ytiles,
-                int total_ytiles, unsigned flags, u64* part5, int64_t* cand, int cand_is_out_layout, cudaStream_t stream) {
+                int total_ytiles, unsigned flags, u64* part5, int64_t* cand, int cand_is_out_layout, cudaStream_t stream,
+                const TCPlan* tc) {
     if (total_items <= 0 || total_ytiles <= 0) return 0;
     NNParams prm;
     prm.pairs = pairs_dev; prm.npairs = npairs; prm.uniform_items = uniform_items; prm.k = k;
     prm.nx = nx; prm.ny = ny; prm.best = nullptr; prm.part5 = part5; prm.best2 = nullptr; prm.ncols = nullptr;
     prm.tileflag = nullptr; prm.tilecnt = nullptr; prm.out = nullptr; prm.flags = flags;
     int rc;
-    if (nn_path() == PATH_GATED) {
+    if (tc) {
+        // the screen + verification write nn_query's candidates for every column tile they can decide; the gated
+        // kernel, its exact fallback and the merge below then only touch the flagged tiles
+        if ((rc = launch_tc(1, xT, ld1_total, nx, yT, ld2_total, ny, k, pairs_dev, npairs, tc->uni_items, tc->total_items,
+                            tc->uni_xtiles, tc->total_xtiles, uniform_ytiles, total_ytiles, tc->ld1_tc_total, flags, nullptr,
+                            cand, cand_is_out_layout, tc->ws, stream))) return rc;
+    }
+    const int* tc_only = tc ? tc->ws.tcflag : nullptr;
+    if (tc || nn_path() == PATH_GATED) {
         // tile flags follow the partial lists in the workspace (top5_ws_bytes)
         prm.tileflag = reinterpret_cast<int*>(part5 + (size_t)total_items * TILE * 5);
         F2P_CUDA(cudaMemsetAsync(prm.tileflag, 0, sizeof(int) * (size_t)total_ytiles, stream));
+        prm.ncols = tc_only;
         if ((rc = launch_gated<5>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream))) return rc;
+        prm.ncols = nullptr;
     }
     rc = launch_mode<1>(xT, ld1_total, yT, ld2_total, k, prm, total_items, stream);   // gated path: flagged tiles only
     if (rc) return rc;
-    finalize_top5_kernel<<<total_ytiles, TILE, 0, stream>>>(part5, pairs_dev, npairs, uniform_ytiles, flags, cand, cand_is_out_layout);
+    finalize_top5_kernel<<<total_ytiles, TILE, 0, stream>>>(part5, pairs_dev, npairs, uniform_ytiles, flags, cand,
+                                                            cand_is_out_layout, tc_only);
     F2P_CUDA(cudaGetLastError());
     return 0;
 }

@@ -206,6 +206,16 @@ int f2p_spatial_host(const float* C_host, const float* evecs_x_host, int n1, con
  * runs ~ms of pure FMA work and returns TFLOP/s (roofline denominator next to the nominal figure). */
 int f2p_measure_fp32_peak(double* tflops_packed, double* tflops_scalar, void* stream);
 
+/* Measured TF32 tensor-pipe throughput of this device with the instruction shape of the kernel-2 screen (tcgen05.mma
+ * kind::tf32, M128 N256 K8, operands in shared memory): TFLOP/s, the roofline denominator of csrc/tc.cu. */
+int f2p_measure_tf32_peak(double* tflops, void* stream);
+
+/* Counters of the most recent tensor-pipe screen (synchronous read; measurement aid, no reference counterpart):
+ * out[0] candidates recorded by the screen, out[1] candidate lists that overflowed (their column tiles were redone by the
+ * FP32 kernels), out[2] candidates re-evaluated exactly, out[3] re-evaluated candidates whose tensor-pipe lower bound
+ * exceeded the exact value (must be 0: the run-time check of the error-band assumptions), out[4..7] reserved. */
+int f2p_tc_last_stats(unsigned long long out[8]);
+
 /* Stage timing of f2p_naive_batched / f2p_spatial_batched for the per-kernel roofline of bench.py (measurement aid; no
  * reference counterpart).  Off by default; when on, the two entry points record CUDA events on the caller's stream at
  * their stage boundaries (one timed call at a time).  f2p_stage_times waits for the last timed call and returns
