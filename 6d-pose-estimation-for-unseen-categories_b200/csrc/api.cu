@@ -156,7 +156,7 @@ static int build_plan(const F2PPairDesc* d, int npairs, int k, int spatial, bool
     }
     // tensor-pipe screen: its own row tiling (256-row tiles, one CTA per SM)
     P.spatial = spatial;
-    P.use_tc = npairs > 0 && tc_enabled(P.flops, k);
+    P.use_tc = npairs > 0 && tc_enabled(P.flops, k, spatial);
     P.tc = TCPlan();
     if (P.use_tc) {
         int64_t rows = 0, items = 0, xt = 0;

@@ -31,8 +31,8 @@ int sm_count_now() {
 int pick_nsplit(int nrt, int nct) { return choose_nsplit(nct, nrt, sm_count_now()); }
 
 // tensor-pipe screen geometry of a single pair (tc.cu); returns false when the screen is not used for this shape
-bool single_pair_tc(PairDev& p, int k, TCPlan& tc) {
-    if (!tc_enabled(2.0 * p.n1 * (double)p.n2 * k, k)) return false;
+bool single_pair_tc(PairDev& p, int k, int top5, TCPlan& tc) {
+    if (!tc_enabled(2.0 * p.n1 * (double)p.n2 * k, k, top5)) return false;
     p.tc_nrt = (p.n1 + TC_ROWS - 1) / TC_ROWS;
     p.tc_nsplit = choose_tc_nsplit(p.nct, p.tc_nrt, sm_count_now());
     p.tc_item0 = 0; p.tc_xtile0 = 0; p.xa_row0 = 0;
@@ -74,7 +74,7 @@ size_t f2p_nn_workspace_bytes(int n1, int n2, int k, int top5) {
     PairDev p; memset(&p, 0, sizeof(p));
     p.n1 = n1; p.n2 = n2; p.nct = nct;
     TCPlan tc;
-    if (n1 >= 1 && n2 >= 1 && single_pair_tc(p, k, tc))
+    if (n1 >= 1 && n2 >= 1 && single_pair_tc(p, k, top5, tc))
         b += tc_ws_bytes(tc.ld1_tc_total, (int64_t)nct * TILE, k, tc.total_items, nct, 1, top5);
     return (b + 255) & ~(size_t)255;
 }
@@ -99,7 +99,7 @@ static int nn_common(int mode, const float* xT, const float* nx, int n1, int ld1
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int items = p.nct * p.nsplit;
     TCPlan tc;
-    const bool use_tc = ld2 == nct * TILE && single_pair_tc(p, k, tc);
+    const bool use_tc = ld2 == nct * TILE && single_pair_tc(p, k, mode, tc);
     if (use_tc) {
         size_t off = 256 + (mode ? top5_ws_bytes(items, p.nct) : argmin_ws_bytes(ld2, k, 1));
         off = (off + 255) & ~(size_t)255;

@@ -72,7 +72,7 @@ int launch_top5(const float* xT, int64_t ld1_total, const float* nx, const float
 constexpr int TC_ROWS = 256;   // CAD rows per accumulator tile of the screen
 constexpr int TC_EH = 2;       // epilogue threads per scene point (4 * TC_EH epilogue warps)
 struct TCWs {
-    float* XA; float* YA; uint32_t* tau; unsigned long long* cand; int* ccnt;
+    float* XA; float* XR; float* YA; uint32_t* tau; unsigned long long* cand; int* ccnt;
     unsigned char* zero_base; size_t zero_bytes;      // stats | nxmax | tcflag | pair_bad, cleared per call
     unsigned long long* stats; uint32_t* nxmax; int* tcflag; int* pair_bad;
 };
@@ -111,7 +111,8 @@ static inline int choose_tc_nsplit(long long base_items, int nrt, int sm) {
 // Tensor-pipe path selection (F2P_NN_PATH=tc forces it, =gated / exact / two_phase disable it): by default problems with
 // at least TC_MIN_FLOPS of distance work whose k fills a 128-byte swizzle row.  Non-semantic: every path is exact.
 constexpr double TC_MIN_FLOPS = 4.0e10;
-bool tc_enabled(double flops, int k);
+bool tc_enabled(double flops, int k, int top5);
+bool tc_fits(int k, int top5);   // the resident scene tile + a >= 2-deep ring fit one SM's shared memory
 int measure_tf32_peak(double* tflops, cudaStream_t st);
 int tc_last_stats(unsigned long long out[8]);
 

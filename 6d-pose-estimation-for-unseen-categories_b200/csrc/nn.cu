@@ -987,8 +987,8 @@ static NNPath nn_path() {
 }
 // "tc": tensor-pipe screen in front of the gated kernels regardless of size; "gated" / "exact" / "two_phase": never;
 // unset: by size.  Every choice gives the same (exact) result.
-bool tc_enabled(double flops, int k) {
-    if (tc_kp(k) < 32) return false;          // the packed rows must fill one 128-byte swizzle row
+bool tc_enabled(double flops, int k, int top5) {
+    if (tc_kp(k) < 32 || !tc_fits(k, top5)) return false;   // the packed rows must fill one 128-byte swizzle row
     const char* e = getenv("F2P_NN_PATH");
     if (e && e[0] == 't' && e[1] == 'c') return true;
     if (e && e[0]) return false;

@@ -110,9 +110,12 @@ __device__ __forceinline__ bool mbar_try(uint64_t* bar, uint32_t parity) {
 }
 __device__ __forceinline__ void mbar_wait_tc(uint64_t* bar, uint32_t parity) {
     if (mbar_try(bar, parity)) return;
-    const long long t0 = clock64();
-    while (!mbar_try(bar, parity)) {
-        if (clock64() - t0 > 4000000000ll) { printf("f2p tc: mbarrier timeout (block %d thread %d)\n", blockIdx.x, threadIdx.x); __trap(); }
+    long long t0 = 0;
+    for (unsigned n = 1; !mbar_try(bar, parity); ++n) {
+        if ((n & 255u) == 0) {       // try_wait suspends the thread in hardware; the clock is only a watchdog
+            if (t0 == 0) t0 = clock64();
+            else if (clock64() - t0 > 4000000000ll) { printf("f2p tc: mbarrier timeout (block %d thread %d)\n", blockIdx.x, threadIdx.x); __trap(); }
+        }
     }
 }
 
@@ -384,7 +387,8 @@ __device__ __forceinline__ void tc_insert5(u64 (&l)[5], u64 key) {
 struct TCVerifyParams {
     const PairDev* pairs; int npairs; int uniform_ytiles;
     int k, eh, cap;
-    const float* xT; int64_t ld1_total; const float* nx;
+    const float* XR;        // [ld1_tc_total][k] exact FP32 rows of -2*feat_x (row-major copy made by the packing kernel)
+    const float* nx;
     const float* yT; int64_t ld2_total; const float* ny;
     const uint32_t* tau; const u64* cand; const int* ccnt; const int* tcflag;
     u64* best;              // K = 1: merge keys of the arg-min
@@ -421,10 +425,21 @@ nn_tc_verify_kernel(const TCVerifyParams prm) {
             const u64 ce = cl[(size_t)e * TILE];
             if ((uint32_t)(ce >> 32) >= tau) continue;            // LB >= final threshold: cannot be among the K best
             const uint32_t i = (uint32_t)(ce & 0xffffffffull);
-            const float* xp = prm.xT + (int64_t)pd->x_col0 + i;
+            const float* xp = prm.XR + ((int64_t)pd->xa_row0 + i) * k;      // 4k contiguous bytes: a few cache lines
             float acc = 0.f;
+            if ((k & 3) == 0) {
+#pragma unroll 4
+                for (int c = 0; c < k; c += 4) {
+                    const float4 xv = __ldg(reinterpret_cast<const float4*>(xp + c));
+                    acc = fmaf(xv.x, __ldg(yp + (int64_t)c * prm.ld2_total), acc);
+                    acc = fmaf(xv.y, __ldg(yp + (int64_t)(c + 1) * prm.ld2_total), acc);
+                    acc = fmaf(xv.z, __ldg(yp + (int64_t)(c + 2) * prm.ld2_total), acc);
+                    acc = fmaf(xv.w, __ldg(yp + (int64_t)(c + 3) * prm.ld2_total), acc);
+                }
+            } else {
 #pragma unroll 8
-            for (int c = 0; c < k; ++c) acc = fmaf(__ldg(xp + (int64_t)c * prm.ld1_total), __ldg(yp + (int64_t)c * prm.ld2_total), acc);
+                for (int c = 0; c < k; ++c) acc = fmaf(__ldg(xp + c), __ldg(yp + (int64_t)c * prm.ld2_total), acc);
+            }
             const float v = __fadd_rn(__fadd_rn(acc, __ldg(prm.nx + pd->x_col0 + i)), nyj);
             ++nver;
             if (dec_f((uint32_t)(ce >> 32)) > v) ++nviol;         // the lower bound must hold: assumption A's run-time check
@@ -463,7 +478,8 @@ template <bool IS_X>
 __global__ void __launch_bounds__(256)
 tc_pack_kernel(const float* __restrict__ srcT, int64_t ld_total, const float* __restrict__ nrm,
                const PairDev* __restrict__ pairs, int npairs, int uniform_tiles, int k, int kp, float one_minus_eps,
-               float* __restrict__ dst, uint32_t* __restrict__ nxmax, uint32_t* __restrict__ tau, int* __restrict__ pair_bad) {
+               float* __restrict__ dst, float* __restrict__ dst_exact, uint32_t* __restrict__ nxmax, uint32_t* __restrict__ tau,
+               int* __restrict__ pair_bad) {
     __shared__ float s[TC_KB * PACK_LD];
     __shared__ float s_aug[3][TILE];
     __shared__ float s_live[TILE];
@@ -534,6 +550,7 @@ tc_pack_kernel(const float* __restrict__ srcT, int64_t ld_total, const float* __
                 else v = 0.f;
                 if (!IS_X && !live) v = 0.f;
                 dst[(dst_row0 + r) * kp + c] = v;
+                if (IS_X && c < k) dst_exact[(dst_row0 + r) * k + c] = s[lane * PACK_LD + r];
             }
         }
     }
@@ -630,12 +647,18 @@ static size_t tc_smem_bytes(int kp, int eh, int cap, int* nstage_out) {
     const int nkb = (kp + TC_KB - 1) / TC_KB;
     const size_t fixed = (size_t)nkb * TC_A_BLOCK * sizeof(float) + (size_t)eh * cap * TILE * sizeof(u64) + 24 * sizeof(uint64_t);
     const size_t budget = 227 * 1024 - 1024;            // dynamic shared memory is 1024-aligned by the declaration
-    int S = (int)((budget - fixed) / (TC_B_STAGE * sizeof(float)));
+    int S = fixed >= budget ? 0 : (int)((budget - fixed) / (TC_B_STAGE * sizeof(float)));
     if (S > 6) S = 6;
     *nstage_out = S;
     size_t b = fixed + (size_t)S * TC_B_STAGE * sizeof(float);
     if (b < 120 * 1024) b = 120 * 1024;                 // one CTA per SM: it owns all 512 TMEM columns
     return b;
+}
+
+bool tc_fits(int k, int top5) {
+    int S = 0;
+    tc_smem_bytes(tc_kp(k), TC_EH, top5 ? TCCfg<5>::CAP : TCCfg<1>::CAP, &S);
+    return S >= 2;
 }
 
 size_t tc_ws_bytes(int64_t ld1_tc_total, int64_t ld2_total, int k, int64_t tc_items, int64_t total_ytiles, int npairs, int top5) {
@@ -644,6 +667,7 @@ size_t tc_ws_bytes(int64_t ld1_tc_total, int64_t ld2_total, int k, int64_t tc_it
     size_t b = 0;
     auto add = [&](size_t n) { b += (n + 255) & ~(size_t)255; };
     add(sizeof(float) * (size_t)ld1_tc_total * kp);                 // XA
+    add(sizeof(float) * (size_t)ld1_tc_total * k);                  // XR
     add(sizeof(float) * (size_t)ld2_total * kp);                    // YA
     add(sizeof(uint32_t) * (size_t)ld2_total);                      // tau
     add(sizeof(u64) * (size_t)tc_items * TC_EH * cap * TILE);       // cand
@@ -659,6 +683,7 @@ void tc_ws_carve(TCWs& w, unsigned char* base, int64_t ld1_tc_total, int64_t ld2
     unsigned char* p = base;
     auto take = [&](size_t n) { unsigned char* q = p; p += (n + 255) & ~(size_t)255; return q; };
     w.XA = reinterpret_cast<float*>(take(sizeof(float) * (size_t)ld1_tc_total * kp));
+    w.XR = reinterpret_cast<float*>(take(sizeof(float) * (size_t)ld1_tc_total * k));
     w.YA = reinterpret_cast<float*>(take(sizeof(float) * (size_t)ld2_total * kp));
     w.tau = reinterpret_cast<uint32_t*>(take(sizeof(uint32_t) * (size_t)ld2_total));
     w.cand = reinterpret_cast<u64*>(take(sizeof(u64) * (size_t)tc_items * TC_EH * cap * TILE));
@@ -704,9 +729,9 @@ int launch_tc(int top5, const float* xT, int64_t ld1_total, const float* nx, con
     F2P_CUDA(cudaMemsetAsync(w.zero_base, 0, w.zero_bytes, stream));
     g_last_stats = w.stats;
     tc_pack_kernel<true><<<total_tc_xtiles, 256, 0, stream>>>(xT, ld1_total, nx, pairs_dev, npairs, uniform_tc_xtiles, k, kp,
-                                                             ome, w.XA, w.nxmax, nullptr, w.pair_bad);
+                                                             ome, w.XA, w.XR, w.nxmax, nullptr, w.pair_bad);
     tc_pack_kernel<false><<<total_ytiles, 256, 0, stream>>>(yT, ld2_total, ny, pairs_dev, npairs, uniform_ytiles, k, kp,
-                                                           ome, w.YA, nullptr, w.tau, w.pair_bad);
+                                                           ome, w.YA, nullptr, nullptr, w.tau, w.pair_bad);
     F2P_CUDA(cudaGetLastError());
 
     CUtensorMap mapXA, mapYA;
@@ -726,7 +751,7 @@ int launch_tc(int top5, const float* xT, int64_t ld1_total, const float* nx, con
     TCVerifyParams vp;
     vp.pairs = pairs_dev; vp.npairs = npairs; vp.uniform_ytiles = uniform_ytiles; vp.k = k; vp.eh = TC_EH;
     vp.cap = top5 ? TCCfg<5>::CAP : TCCfg<1>::CAP;
-    vp.xT = xT; vp.ld1_total = ld1_total; vp.nx = nx; vp.yT = yT; vp.ld2_total = ld2_total; vp.ny = ny;
+    vp.XR = w.XR; vp.nx = nx; vp.yT = yT; vp.ld2_total = ld2_total; vp.ny = ny;
     vp.tau = w.tau; vp.cand = w.cand; vp.ccnt = w.ccnt; vp.tcflag = w.tcflag; vp.best = best; vp.out5 = out5;
     vp.cand_is_out_layout = cand_is_out_layout; vp.flags = flags; vp.stats = w.stats;
     if (top5) nn_tc_verify_kernel<5><<<total_ytiles, TILE, 0, stream>>>(vp);

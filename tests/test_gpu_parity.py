@@ -32,17 +32,19 @@ def oracle():
     return O
 
 
-@pytest.fixture(params=["gated", "exact", "two_phase"])
+@pytest.fixture(params=["gated", "exact", "two_phase", "tc"])
 def argmin_path(request, monkeypatch):
-    """Runs a test through every arg-min path: the threshold-gated kernel (default), the exact kernel alone, and the
-    raw pass + re-check of sqrt-ambiguous columns."""
+    """Runs a test through every arg-min path: the threshold-gated kernel (default for small problems), the exact kernel
+    alone, the raw pass + re-check of sqrt-ambiguous columns, and the tensor-pipe screen + exact verification (default
+    for large problems; forced here at every size whose k fills a swizzle row)."""
     monkeypatch.setenv("F2P_NN_PATH", request.param)
     return request.param
 
 
-@pytest.fixture(params=["gated", "exact"])
+@pytest.fixture(params=["gated", "exact", "tc"])
 def top5_path(request, monkeypatch):
-    """Runs a spatial test through the threshold-gated top-5 kernel (default) and the exact register-list kernel."""
+    """Runs a spatial test through the threshold-gated top-5 kernel, the exact register-list kernel and the tensor-pipe
+    screen + exact verification."""
     monkeypatch.setenv("F2P_NN_PATH", request.param)
     return request.param
 
