@@ -164,11 +164,11 @@ static int build_plan(const F2PPairDesc* d, int npairs, int k, int spatial, bool
             PairDev& p = P.pairs[i];
             p.tc_nrt = (p.n1 + TC_ROWS - 1) / TC_ROWS;
             p.tc_nsplit = choose_tc_nsplit(base_items, p.tc_nrt, sm_count());
-            if (rows + (int64_t)p.tc_nrt * TC_ROWS > 0x7fffff00ll || items + (int64_t)p.nct * p.tc_nsplit > 0x7fffff00ll) {
+            if (rows + (int64_t)p.tc_nrt * TC_ROWS > 0x7fffff00ll || (items + (int64_t)p.nct * p.tc_nsplit) * TC_CG > 0x7fffff00ll) {
                 set_error("batch too large for 32-bit tile indexing; split the batch"); return F2P_ENOTSUP;
             }
             p.xa_row0 = (int)rows; p.tc_item0 = (int)items; p.tc_xtile0 = (int)xt;
-            rows += (int64_t)p.tc_nrt * TC_ROWS; items += (int64_t)p.nct * p.tc_nsplit; xt += 2 * p.tc_nrt;
+            rows += (int64_t)p.tc_nrt * TC_ROWS; items += (int64_t)((p.nct + TC_CG - 1) / TC_CG) * p.tc_nsplit; xt += 2 * p.tc_nrt;
         }
         P.tc.ld1_tc_total = rows; P.tc.total_items = (int)items; P.tc.total_xtiles = (int)xt;
     }
@@ -182,7 +182,7 @@ static int build_plan(const F2PPairDesc* d, int npairs, int k, int spatial, bool
     P.uni_ytiles = uniform([](const PairDev& p) { return p.nct; });
     P.uni_items = uniform([](const PairDev& p) { return p.nct * p.nsplit; });
     if (P.use_tc) {
-        P.tc.uni_items = uniform([](const PairDev& p) { return p.nct * p.tc_nsplit; });
+        P.tc.uni_items = uniform([](const PairDev& p) { return ((p.nct + TC_CG - 1) / TC_CG) * p.tc_nsplit; });
         P.tc.uni_xtiles = uniform([](const PairDev& p) { return 2 * p.tc_nrt; });
     }
 

@@ -36,7 +36,7 @@ bool single_pair_tc(PairDev& p, int k, int top5, TCPlan& tc) {
     p.tc_nrt = (p.n1 + TC_ROWS - 1) / TC_ROWS;
     p.tc_nsplit = choose_tc_nsplit(p.nct, p.tc_nrt, sm_count_now());
     p.tc_item0 = 0; p.tc_xtile0 = 0; p.xa_row0 = 0;
-    tc.total_items = tc.uni_items = p.nct * p.tc_nsplit;
+    tc.total_items = tc.uni_items = ((p.nct + TC_CG - 1) / TC_CG) * p.tc_nsplit;
     tc.total_xtiles = tc.uni_xtiles = 2 * p.tc_nrt;
     tc.ld1_tc_total = (int64_t)p.tc_nrt * TC_ROWS;
     return true;

@@ -71,6 +71,7 @@ int launch_top5(const float* xT, int64_t ld1_total, const float* nx, const float
 // tc.cu — tensor-pipe (tcgen05, TF32) screen + exact verification of kernel 2
 constexpr int TC_ROWS = 256;   // CAD rows per accumulator tile of the screen
 constexpr int TC_EH = 2;       // epilogue threads per scene point (4 * TC_EH epilogue warps)
+constexpr int TC_CG = 2;       // CTAs per MMA (cta_group): 2 = CTA pairs, each item covers two adjacent column tiles
 struct TCWs {
     float* XA; float* XR; float* YA; uint32_t* tau; unsigned long long* cand; int* ccnt;
     unsigned char* zero_base; size_t zero_bytes;      // stats | nxmax | tcflag | pair_bad, cleared per call
@@ -95,7 +96,7 @@ int launch_tc(int top5, const float* xT, int64_t ld1_total, const float* nx, con
 // Row splits per column tile of the screen (one CTA per SM, each owning all of TMEM): whole waves on `sm` SMs, every
 // item streaming >= 8 tiles of 256 rows when the problem allows (per-CTA fixed cost ~ 2.5 tile times: TMEM allocation,
 // barrier init, the resident scene tile, pipeline fill and drain).
-static inline int choose_tc_nsplit(long long base_items, int nrt, int sm) {
+static inline int choose_tc_nsplit(long long base_items, int nrt, int sm) {   // base_items: column tiles (CTAs per row split)
     if (base_items <= 0 || nrt <= 1) return 1;
     long long cap = nrt / 8 > 0 ? nrt / 8 : 1;
     if (base_items * cap < sm) cap = nrt / 2 > 0 ? nrt / 2 : 1;      // tiny problems: fill the SMs first

@@ -87,6 +87,59 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
+// ---- CTA-pair (cta_group::2) variants: one MMA spans two SMs, each CTA holds its own 128 scene points (M half) and
+// half of the streamed CAD rows (N half); the leader CTA (cluster rank 0) issues, both CTAs feed and drain -----------
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_alloc512_2sm(uint32_t* slot) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "r"(512u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_free512_2sm(uint32_t taddr) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(512u) : "memory");
+}
+__device__ __forceinline__ void umma_tf32_2sm(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// arrives on the barrier at this shared-memory offset in BOTH CTAs of the pair
+__device__ __forceinline__ void umma_commit_2sm(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+// TMA load into this CTA's shared memory whose bytes complete on the LEADER CTA's barrier (peer bit of the address cleared)
+__device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar) & 0xfeffffffu), "r"(c0), "r"(c1) : "memory");
+}
+// arrive on the barrier at the same offset in cluster rank `cta` (default .release.cta semantics: the explicit
+// .release.cluster form compiles to MEMBAR.ALL.GPU + ERRBAR, which cost the epilogue warps a third of their time — ncu;
+// the hand-over of a TMEM buffer is ordered by tcgen05.fence::before_thread_sync, not by a memory fence)
+__device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t cta) {
+    asm volatile(
+        "{\n\t.reg .b32 ra;\n\t"
+        "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+        "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}" ::"r"(smem_u32(bar)), "r"(cta) : "memory");
+}
+
+// true in exactly one lane of the (fully active) warp; keeps the surrounding control flow warp-uniform so that the
+// descriptors of tcgen05.mma / TMA stay in uniform registers (a `lane == 0` branch makes the compiler wrap every such
+// instruction in a uniformisation loop: the single issuing thread then needs ~1000 cycles per 4-MMA stage — ncu, v1)
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred = 0;
+    asm volatile(
+        "{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\t"
+        "elect.sync rx|px, %1;\n\t"
+        "@px mov.s32 %0, 1;\n\t}" : "+r"(pred) : "r"(0xffffffffu));
+    return pred != 0;
+}
+
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): start address >> 4, leading byte
@@ -141,21 +194,29 @@ template <int K> struct TCCfg { static constexpr int CAP = (K == 1) ? 16 : 32; }
 // ---------------------------------------------------------------------------------------------------------------
 // Screen kernel.  Warp 0 lane 0: TMA producer; warp 1: TMEM allocation, lane 0 issues the MMAs; warps 2..2+EW:
 // epilogue (TMEM lane quarter = warp % 4; with EW = 8 two warps share a quarter and split the accumulator's columns).
+// CG = 2: the two CTAs of a cluster form one cta_group::2 MMA (M = 256 = two scene tiles, N = 256): each CTA keeps its
+// own scene tile resident and stages only HALF of every CAD tile, so L2 -> SM traffic and shared-memory reads per MMA are
+// halved (the single-CTA form is L2-bandwidth bound: ncu, profiles/r02_ncu_tc_screen_large_v1_summary.txt).  The leader
+// (cluster rank 0) owns the `full` and `tempty` barriers and issues every MMA; tcgen05.commit multicasts to the `empty`
+// / `tfull` barriers of both CTAs.
 // ---------------------------------------------------------------------------------------------------------------
-template <int K, int EW>
+template <int K, int EW, int CG>
 __global__ void __launch_bounds__(64 + 32 * EW, 1)
 nn_tc_screen_kernel(const __grid_constant__ CUtensorMap mapXA, const __grid_constant__ CUtensorMap mapYA, const TCParams prm) {
     constexpr int CAP = TCCfg<K>::CAP;
     constexpr int EH = EW / 4;                 // epilogue threads per scene point (column halves of the accumulator)
     constexpr int CHUNKS = TC_N / 32 / EH;     // 32-column chunks per epilogue thread and tile
+    constexpr int NB = TC_N / CG;              // CAD rows this CTA stages per tile
+    constexpr int B_STAGE = NB * TC_KB;        // floats per stage
+    constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_N >> 3) << 17) | ((uint32_t)((TILE * CG) >> 4) << 24);
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     const int kp = prm.kp;
     const int nkb = (kp + TC_KB - 1) / TC_KB;
     const int last_steps = (kp - (nkb - 1) * TC_KB) / 8;
     const int S = prm.nstage;
     float* sA = reinterpret_cast<float*>(smem_raw);                     // [nkb][128][32]  (SW128)
-    float* sB = sA + (size_t)nkb * TC_A_BLOCK;                          // [S][256][32]    (SW128)
-    u64* s_list = reinterpret_cast<u64*>(sB + (size_t)S * TC_B_STAGE);  // [EH][CAP][TILE]
+    float* sB = sA + (size_t)nkb * TC_A_BLOCK;                          // [S][NB][32]     (SW128)
+    u64* s_list = reinterpret_cast<u64*>(sB + (size_t)S * B_STAGE);     // [EH][CAP][TILE]
     uint64_t* bars = reinterpret_cast<uint64_t*>(s_list + (size_t)EH * CAP * TILE);
     uint64_t* fullA = bars;             // 1
     uint64_t* full = bars + 1;          // S (<= 8)
@@ -163,85 +224,108 @@ nn_tc_screen_kernel(const __grid_constant__ CUtensorMap mapXA, const __grid_cons
     uint64_t* tfull = bars + 17;        // 2
     uint64_t* tempty = bars + 19;       // 2
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 21);
-    int* s_ovf = reinterpret_cast<int*>(s_tmem + 1);
+    int* s_flag = reinterpret_cast<int*>(s_tmem + 1);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int item = blockIdx.x;
+    const uint32_t rank = (CG == 2) ? cluster_ctarank() : 0u;
+    const bool leader = rank == 0;
+    const int item = blockIdx.x / CG;
     const int pi = find_pair(item, prm.pairs, prm.npairs, prm.uniform_items, &PairDev::tc_item0);
     const PairDev* pdp = prm.pairs + pi;
-    const int nsplit = pdp->tc_nsplit, nrt = pdp->tc_nrt, n2 = pdp->n2;
+    const int nsplit = pdp->tc_nsplit, nrt = pdp->tc_nrt, n2 = pdp->n2, nct = pdp->nct;
     const int local = item - pdp->tc_item0;
-    const int ct = local / nsplit, sp = local - ct * nsplit;
+    const int ctp = local / nsplit, sp = local - ctp * nsplit;
+    const int ct_raw = ctp * CG + (int)rank;
+    const bool dummy = ct_raw >= nct;          // odd tile count: the pair's last cluster has one idle half
+    const int ct = dummy ? nct - 1 : ct_raw;   // (it still stages its half of the CAD rows and keeps the barriers going)
     const int t_begin = (int)(((long long)sp * nrt) / nsplit);
     const int t_end = (int)(((long long)(sp + 1) * nrt) / nsplit);
     const int ntiles = t_end - t_begin;
     const int xrow0 = pdp->xa_row0, ycol = pdp->y_col0 + ct * TILE;
     const int ytile = pdp->ytile0 + ct;
+    const size_t slot = (size_t)item * CG + rank;      // candidate lists of this CTA
 
-    // a pair outside the proven operand range, or a tile another CTA already gave up on: leave it to the FFMA2 kernels
-    // (one thread reads the flags so that the whole CTA takes the same decision)
+    // a pair outside the proven operand range is left to the FFMA2 kernels (same decision in both CTAs of a cluster:
+    // the flag was written by the packing kernels)
     if (tid == 0) {
         const int bad = prm.pair_bad[pi];
-        if (bad) prm.tcflag[ytile] = 1;
-        *s_ovf = bad | *reinterpret_cast<volatile int*>(prm.tcflag + ytile);
+        if (bad && !dummy) prm.tcflag[ytile] = 1;
+        *s_flag = bad;
     }
     __syncthreads();
-    if (*s_ovf) return;
+    if (*s_flag) return;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&mapXA);
         tma_prefetch_desc(&mapYA);
         mbar_init(fullA, 1);
         for (int s = 0; s < S; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-        for (int b = 0; b < 2; ++b) { mbar_init(&tfull[b], 1); mbar_init(&tempty[b], EW); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&tfull[b], 1); mbar_init(&tempty[b], EW * CG); }
         fence_barrier_init();
     }
-    if (warp == 1) tmem_alloc512(s_tmem);
+    if (warp == 1) { if (CG == 2) tmem_alloc512_2sm(s_tmem); else tmem_alloc512(s_tmem); }
     tc_fence_before();
-    __syncthreads();
+    if (CG == 2) cluster_sync_all(); else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *s_tmem;
 
     if (warp == 0) {
-        if (lane == 0) {
-            // ---- TMA producer ----
-            mbar_arrive_expect_tx(fullA, (uint32_t)(nkb * TC_A_BLOCK * sizeof(float)));
-            for (int kb = 0; kb < nkb; ++kb) tma_load_2d(sA + (size_t)kb * TC_A_BLOCK, &mapYA, kb * TC_KB, ycol, fullA);
-            int it = 0;
-            for (int t = 0; t < ntiles; ++t) {
-                const int row = xrow0 + (t_begin + t) * TC_N;
-                for (int kb = 0; kb < nkb; ++kb, ++it) {
-                    const int s = it % S;
-                    mbar_wait_tc(&empty[s], (uint32_t)(((it / S) & 1) ^ 1));
-                    mbar_arrive_expect_tx(&full[s], (uint32_t)(TC_B_STAGE * sizeof(float)));
-                    tma_load_2d(sB + (size_t)s * TC_B_STAGE, &mapXA, kb * TC_KB, row, &full[s]);
+        // ---- TMA producer (both CTAs; the leader arms the barriers with the bytes of the whole pair).  The whole warp
+        // walks the loop (uniform control flow), one elected lane issues. ----
+        if (elect_one()) {
+            if (leader) mbar_arrive_expect_tx(fullA, (uint32_t)(CG * nkb * TC_A_BLOCK * sizeof(float)));
+            for (int kb = 0; kb < nkb; ++kb) {
+                if (CG == 2) tma_load_2d_2sm(sA + (size_t)kb * TC_A_BLOCK, &mapYA, kb * TC_KB, ycol, fullA);
+                else tma_load_2d(sA + (size_t)kb * TC_A_BLOCK, &mapYA, kb * TC_KB, ycol, fullA);
+            }
+        }
+        __syncwarp();
+        int s = 0; uint32_t ph = 1;          // waiting on parity 1 of a fresh barrier returns at once
+        for (int t = 0; t < ntiles; ++t) {
+            const int row = xrow0 + (t_begin + t) * TC_N + (int)rank * NB;
+            for (int kb = 0; kb < nkb; ++kb) {
+                mbar_wait_tc(&empty[s], ph);
+                if (elect_one()) {
+                    if (leader) mbar_arrive_expect_tx(&full[s], (uint32_t)(CG * B_STAGE * sizeof(float)));
+                    if (CG == 2) tma_load_2d_2sm(sB + (size_t)s * B_STAGE, &mapXA, kb * TC_KB, row, &full[s]);
+                    else tma_load_2d(sB + (size_t)s * B_STAGE, &mapXA, kb * TC_KB, row, &full[s]);
                 }
+                __syncwarp();
+                if (++s == S) { s = 0; ph ^= 1u; }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ---- MMA issuer ----
+        if (leader) {
+            // ---- MMA issuer: warp-uniform loop, descriptors advanced by adding to their address field ----
             mbar_wait_tc(fullA, 0);
-            const uint32_t a_base = smem_u32(sA), b_base = smem_u32(sB);
-            int it = 0;
+            const uint64_t a_desc0 = smem_desc_sw128(smem_u32(sA)), b_desc0 = smem_desc_sw128(smem_u32(sB));
+            constexpr uint32_t A_BLK16 = (uint32_t)(TC_A_BLOCK * sizeof(float)) >> 4, B_STG16 = (uint32_t)(B_STAGE * sizeof(float)) >> 4;
+            int s = 0; uint32_t ph = 0;
             for (int t = 0; t < ntiles; ++t) {
                 const int buf = t & 1;
                 mbar_wait_tc(&tempty[buf], (uint32_t)(((t >> 1) & 1) ^ 1));
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(buf * TC_N);
-                for (int kb = 0; kb < nkb; ++kb, ++it) {
-                    const int s = it % S;
-                    mbar_wait_tc(&full[s], (uint32_t)((it / S) & 1));
+                for (int kb = 0; kb < nkb; ++kb) {
+                    mbar_wait_tc(&full[s], ph);
                     tc_fence_after();
+                    const uint64_t ad = a_desc0 + (uint64_t)((uint32_t)kb * A_BLK16);
+                    const uint64_t bd = b_desc0 + (uint64_t)((uint32_t)s * B_STG16);
                     const int nst = (kb == nkb - 1) ? last_steps : TC_KB / 8;
-                    const uint32_t a0 = a_base + (uint32_t)(kb * TC_A_BLOCK * sizeof(float));
-                    const uint32_t b0 = b_base + (uint32_t)(s * TC_B_STAGE * sizeof(float));
-                    for (int st = 0; st < nst; ++st)
-                        umma_tf32(d_tmem, smem_desc_sw128(a0 + st * 32), smem_desc_sw128(b0 + st * 32), TC_IDESC,
-                                  (uint32_t)((kb | st) != 0));
-                    umma_commit(&empty[s]);        // frees the stage when these MMAs have read it
+                    if (elect_one()) {
+#pragma unroll
+                        for (int st = 0; st < TC_KB / 8; ++st) {
+                            if (st < nst) {
+                                if (CG == 2) umma_tf32_2sm(d_tmem, ad + 2 * st, bd + 2 * st, IDESC, (uint32_t)((kb | st) != 0));
+                                else umma_tf32(d_tmem, ad + 2 * st, bd + 2 * st, IDESC, (uint32_t)((kb | st) != 0));
+                            }
+                        }
+                        if (CG == 2) umma_commit_2sm(&empty[s]); else umma_commit(&empty[s]);   // frees the stage (both CTAs)
+                        if (kb == nkb - 1) { if (CG == 2) umma_commit_2sm(&tfull[buf]); else umma_commit(&tfull[buf]); }   // tile t complete
+                    }
+                    __syncwarp();
+                    if (++s == S) { s = 0; ph ^= 1u; }
                 }
-                umma_commit(&tfull[buf]);          // accumulator of tile t complete
             }
         }
     } else {
@@ -250,7 +334,7 @@ nn_tc_screen_kernel(const __grid_constant__ CUtensorMap mapXA, const __grid_cons
         const int quarter = warp & 3;              // TMEM lanes this warp may read: [32 * (warp % 4), +32)
         const int half = (EH == 2) ? (ew >> 2) : 0;
         const int col = quarter * 32 + lane;       // scene point of this thread within the tile
-        const bool live = ct * TILE + col < n2;
+        const bool live = !dummy && ct * TILE + col < n2;
         u64* my_list = s_list + (size_t)half * CAP * TILE + col;     // entry e at my_list[e * TILE]
         const float nyj = live ? prm.ny[ycol + col] : 0.f;
         const float wy = __fmaf_ru(prm.omega, nyj, 3.1554436e-30f);   // OMEGA * ny + 2^-98
@@ -306,10 +390,10 @@ nn_tc_screen_kernel(const __grid_constant__ CUtensorMap mapXA, const __grid_cons
                 tmem_ld_wait();
                 if (c + 1 < CHUNKS) tmem_ld32(taddr + (uint32_t)((c + 1) * 32), nxt);
                 else {
-                    // all of this thread's reads of the buffer have landed: hand it back to the MMA warp
+                    // all of this thread's reads of the buffer have landed: hand it back to the MMA issuer
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&tempty[buf]);
+                    if (lane == 0) { if (CG == 2) mbar_arrive_remote(&tempty[buf], 0); else mbar_arrive(&tempty[buf]); }
                 }
                 float g[4];
 #pragma unroll
@@ -345,14 +429,14 @@ nn_tc_screen_kernel(const __grid_constant__ CUtensorMap mapXA, const __grid_cons
             if (T < T_in && ub[K - 1] < Tg) { atomicMin(taup, enc_f(ub[K - 1])); }
         }
         // survivors of this CTA: entries still below its final threshold
-        if (live) {
-            compact();
-            u64* gl = prm.cand + ((size_t)(item * EH + half) * CAP) * TILE + col;
-            for (int e = 0; e < cnt; ++e) gl[(size_t)e * TILE] = my_list[e * TILE];
-            prm.ccnt[(size_t)(item * EH + half) * TILE + col] = cnt;
-            if (ovf) prm.tcflag[ytile] = 1;
-        } else {
-            prm.ccnt[(size_t)(item * EH + half) * TILE + col] = 0;
+        if (!dummy) {
+            if (live) {
+                compact();
+                u64* gl = prm.cand + ((slot * EH + half) * CAP) * TILE + col;
+                for (int e = 0; e < cnt; ++e) gl[(size_t)e * TILE] = my_list[e * TILE];
+                if (ovf) prm.tcflag[ytile] = 1;
+            }
+            prm.ccnt[(slot * EH + half) * TILE + col] = live ? cnt : 0;
         }
         if (prm.stats) {
             int tot = nrec;
@@ -363,9 +447,10 @@ nn_tc_screen_kernel(const __grid_constant__ CUtensorMap mapXA, const __grid_cons
         }
     }
 
+    // nobody leaves while the other CTA may still signal this one's barriers or read its shared memory
     tc_fence_before();
-    __syncthreads();
-    if (warp == 1) { tc_fence_after(); tmem_free512(tmem_base); }
+    if (CG == 2) cluster_sync_all(); else __syncthreads();
+    if (warp == 1) { tc_fence_after(); if (CG == 2) tmem_free512_2sm(tmem_base); else tmem_free512(tmem_base); }
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -418,7 +503,9 @@ nn_tc_verify_kernel(const TCVerifyParams prm) {
     unsigned long long nver = 0, nviol = 0;
     const int nsplit = pd->tc_nsplit;
     for (int sh = 0; sh < nsplit * prm.eh; ++sh) {
-        const size_t slot = (size_t)(pd->tc_item0 + ct * nsplit) * prm.eh + sh;
+        // lists of the CTA (item, cluster rank) that screened this column tile for row split sh / eh, accumulator half sh % eh
+        const size_t item = (size_t)pd->tc_item0 + (size_t)(ct / TC_CG) * nsplit + (size_t)(sh / prm.eh);
+        const size_t slot = (item * TC_CG + (size_t)(ct % TC_CG)) * prm.eh + (size_t)(sh % prm.eh);
         const int n = prm.ccnt[slot * TILE + tid];
         const u64* cl = prm.cand + slot * prm.cap * TILE + tid;
         for (int e = 0; e < n; ++e) {
@@ -579,15 +666,18 @@ __global__ void __launch_bounds__(128, 1) tc_peak_kernel(int iters, float* sink)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *s_tmem;
-    if (tid == 0) {
-        const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB);
+    if (warp == 0) {
+        const uint64_t ad = smem_desc_sw128(smem_u32(sA)), bd = smem_desc_sw128(smem_u32(sB));
         for (int it = 0; it < iters; ++it) {
             const uint32_t d = tmem_base + (uint32_t)((it & 1) * TC_N);
+            if (elect_one()) {
 #pragma unroll
-            for (int st = 0; st < 4; ++st)
-                umma_tf32(d, smem_desc_sw128(a0 + st * 32), smem_desc_sw128(b0 + st * 32), TC_IDESC, (uint32_t)(it > 1 || st > 0));
+                for (int st = 0; st < 4; ++st) umma_tf32(d, ad + 2 * st, bd + 2 * st, TC_IDESC, (uint32_t)(it > 1 || st > 0));
+            }
+            __syncwarp();
         }
-        umma_commit(bar);
+        if (elect_one()) umma_commit(bar);
+        __syncwarp();
         mbar_wait_tc(bar, 0);
     }
     tc_fence_before();
@@ -645,12 +735,13 @@ int tc_kp(int k) { return (k + 6 + 7) / 8 * 8; }
 
 static size_t tc_smem_bytes(int kp, int eh, int cap, int* nstage_out) {
     const int nkb = (kp + TC_KB - 1) / TC_KB;
+    const size_t stage = (size_t)(TC_B_STAGE / TC_CG) * sizeof(float);
     const size_t fixed = (size_t)nkb * TC_A_BLOCK * sizeof(float) + (size_t)eh * cap * TILE * sizeof(u64) + 24 * sizeof(uint64_t);
     const size_t budget = 227 * 1024 - 1024;            // dynamic shared memory is 1024-aligned by the declaration
-    int S = fixed >= budget ? 0 : (int)((budget - fixed) / (TC_B_STAGE * sizeof(float)));
-    if (S > 6) S = 6;
+    int S = fixed >= budget ? 0 : (int)((budget - fixed) / stage);
+    if (S > 8) S = 8;
     *nstage_out = S;
-    size_t b = fixed + (size_t)S * TC_B_STAGE * sizeof(float);
+    size_t b = fixed + (size_t)S * stage;
     if (b < 120 * 1024) b = 120 * 1024;                 // one CTA per SM: it owns all 512 TMEM columns
     return b;
 }
@@ -670,8 +761,8 @@ size_t tc_ws_bytes(int64_t ld1_tc_total, int64_t ld2_total, int k, int64_t tc_it
     add(sizeof(float) * (size_t)ld1_tc_total * k);                  // XR
     add(sizeof(float) * (size_t)ld2_total * kp);                    // YA
     add(sizeof(uint32_t) * (size_t)ld2_total);                      // tau
-    add(sizeof(u64) * (size_t)tc_items * TC_EH * cap * TILE);       // cand
-    add(sizeof(int) * (size_t)tc_items * TC_EH * TILE);             // ccnt
+    add(sizeof(u64) * (size_t)tc_items * TC_CG * TC_EH * cap * TILE);       // cand
+    add(sizeof(int) * (size_t)tc_items * TC_CG * TC_EH * TILE);             // ccnt
     add(sizeof(uint32_t) * (size_t)(ld1_tc_total / TC_N) + sizeof(int) * (size_t)(total_ytiles + (npairs > 0 ? npairs : 1)) + 64);   // zeroed block
     return b;
 }
@@ -686,8 +777,8 @@ void tc_ws_carve(TCWs& w, unsigned char* base, int64_t ld1_tc_total, int64_t ld2
     w.XR = reinterpret_cast<float*>(take(sizeof(float) * (size_t)ld1_tc_total * k));
     w.YA = reinterpret_cast<float*>(take(sizeof(float) * (size_t)ld2_total * kp));
     w.tau = reinterpret_cast<uint32_t*>(take(sizeof(uint32_t) * (size_t)ld2_total));
-    w.cand = reinterpret_cast<u64*>(take(sizeof(u64) * (size_t)tc_items * TC_EH * cap * TILE));
-    w.ccnt = reinterpret_cast<int*>(take(sizeof(int) * (size_t)tc_items * TC_EH * TILE));
+    w.cand = reinterpret_cast<u64*>(take(sizeof(u64) * (size_t)tc_items * TC_CG * TC_EH * cap * TILE));
+    w.ccnt = reinterpret_cast<int*>(take(sizeof(int) * (size_t)tc_items * TC_CG * TC_EH * TILE));
     // one zero-initialised block: stats[8] | nxmax[tiles] | tcflag[ytiles] | pair_bad[npairs]
     w.zero_bytes = 64 + sizeof(uint32_t) * (size_t)(ld1_tc_total / TC_N) + sizeof(int) * (size_t)(total_ytiles + (npairs > 0 ? npairs : 1));
     unsigned char* z = take(w.zero_bytes);
@@ -705,9 +796,16 @@ static int launch_screen(const TCWs& w, const CUtensorMap& mapXA, const CUtensor
     const size_t smem = tc_smem_bytes(prm.kp, TC_EH, TCCfg<K>::CAP, &S);
     if (S < 2) { set_error("tensor-pipe screen: k too large for the shared-memory ring"); return F2P_ENOTSUP; }
     prm.nstage = S;
-    F2P_CUDA(cudaFuncSetAttribute(nn_tc_screen_kernel<K, 4 * TC_EH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    nn_tc_screen_kernel<K, 4 * TC_EH><<<total_items, 64 + 32 * 4 * TC_EH, smem, stream>>>(mapXA, mapYA, prm);
-    F2P_CUDA(cudaGetLastError());
+    auto kern = nn_tc_screen_kernel<K, 4 * TC_EH, TC_CG>;
+    F2P_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)total_items * TC_CG); cfg.blockDim = dim3(64 + 32 * 4 * TC_EH);
+    cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = TC_CG; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    F2P_CUDA(cudaLaunchKernelEx(&cfg, kern, mapXA, mapYA, prm));
     return 0;
 }
 
@@ -735,7 +833,7 @@ int launch_tc(int top5, const float* xT, int64_t ld1_total, const float* nx, con
     F2P_CUDA(cudaGetLastError());
 
     CUtensorMap mapXA, mapYA;
-    int rc = make_tensor_map_2d(&mapXA, w.XA, (uint64_t)kp, (uint64_t)ld1_tc_total, (uint64_t)kp, TC_KB, TC_N, 1);
+    int rc = make_tensor_map_2d(&mapXA, w.XA, (uint64_t)kp, (uint64_t)ld1_tc_total, (uint64_t)kp, TC_KB, TC_N / TC_CG, 1);
     if (rc) return rc;
     rc = make_tensor_map_2d(&mapYA, w.YA, (uint64_t)kp, (uint64_t)ld2_total, (uint64_t)kp, TC_KB, TILE, 1);
     if (rc) return rc;
