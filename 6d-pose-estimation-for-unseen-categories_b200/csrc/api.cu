@@ -86,14 +86,16 @@ void stage_filter_counts(int* const* cnt_dev, int npairs) {
     g_stage.cnt.assign(cnt_dev, cnt_dev + npairs);
 }
 
-static int g_sm_count = 0;
+// SM count of the CURRENT device, cached per device id (a process may drive several GPUs)
 static int sm_count() {
-    if (g_sm_count == 0) {
-        int dev = 0, n = 0;
-        if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess) g_sm_count = n;
-        if (g_sm_count <= 0) g_sm_count = 148;
+    static int cache[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cache[dev] == 0) {
+        int n = 0;
+        cache[dev] = (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0) ? n : 148;
     }
-    return g_sm_count;
+    return cache[dev];
 }
 
 // ---- batch plan: host-side decomposition into tiles / work items and the workspace layout --------------

@@ -138,6 +138,8 @@ int f2p_spatial_filter(const float* cad, int ncad, const float* pc, int npc, con
                              static_cast<unsigned char*>(ws), ws_bytes, static_cast<cudaStream_t>(stream));
 }
 
+int f2p_test_vote_band(double band) { set_vote_band_override(band); return 0; }
+
 int f2p_measure_tf32_peak(double* tflops, void* stream) { return measure_tf32_peak(tflops, static_cast<cudaStream_t>(stream)); }
 
 int f2p_tc_last_stats(unsigned long long out[8]) {

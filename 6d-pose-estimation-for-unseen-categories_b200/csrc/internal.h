@@ -134,6 +134,7 @@ int run_filter_batch(const PairDev* pairs_host, int npairs, const float* cad, co
 int run_filter_single(const float* cad, int ncad, const float* pc, int npc, const int64_t* p, int M, const float thr[4],
                       int64_t* out, int32_t* count, int32_t* status, uint8_t* mask, float* scores,
                       unsigned char* ws, size_t ws_bytes, cudaStream_t st);
+void set_vote_band_override(double band);   // test hook (f2p_test_vote_band): < 0 restores the proven band
 // peak.cu
 int measure_fp32_peak(double* packed, double* scalar, cudaStream_t st);
 

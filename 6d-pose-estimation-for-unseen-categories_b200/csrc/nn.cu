@@ -401,7 +401,14 @@ __device__ __forceinline__ void gated_compact(int col, float* s_val, uint32_t* s
         if (r < m) { s_val[r * TILE + col] = raw[r]; s_row[r * TILE + col] = (uint32_t)(key[r] & 0xffffffffull); }
     s_cnt[col] = m;
     kept = m;
-    if (m == K) s_tau[col] = raw[K - 1];
+    // tau = top of the sqrt_rn rounding class of the K-th best, not its raw value: the first tile's bootstrap walks the
+    // rows in interleaved order with a cut between steps, so a LOWER-index row with the same rounded distance as the
+    // held K-th best can still arrive and must pass the gate (the (distance, index) order then prefers it)
+    if (m == K) {
+        const float sk = __fsqrt_rn(raw[K - 1]);
+        const float su = __uint_as_float(__float_as_uint(sk) + 1u);
+        s_tau[col] = __fmul_ru(su, su);
+    }
 }
 
 // NXP: L1 prefetch of the row norms at tile start, load in the epilogue.  FUSE (K == 1): the last CTA of a column tile

@@ -251,15 +251,14 @@ static int launch_project_t(const float* evecs, const float* Cmat, const PairDev
                             u64* best_init = nullptr, int* tilecnt = nullptr) {
     if (Cmat == nullptr) {
         const size_t smem = (size_t)k * ELD * sizeof(float);
-        static bool attr_done = false;
-        if (!attr_done) { F2P_CUDA(cudaFuncSetAttribute(transpose_kernel<IS_X>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024)); attr_done = true; }
+        // (the attribute is per device: set on every launch, as nn.cu does — a process-wide flag broke the second GPU)
+        F2P_CUDA(cudaFuncSetAttribute(transpose_kernel<IS_X>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
         transpose_kernel<IS_X><<<total_tiles, PREP_THREADS, smem, stream>>>(evecs, pairs_dev, npairs, uniform_tiles, k, outT, ld_total, nrm, best_init, tilecnt);
     } else {
         const size_t base = (size_t)k * (ELD + CLD) * sizeof(float);
         const int use_ft = base + (size_t)k * ELD * sizeof(float) <= 112 * 1024;   // keep 2 CTAs per SM
         const size_t smem = base + (use_ft ? (size_t)k * ELD * sizeof(float) : 0);
-        static bool attr_done = false;
-        if (!attr_done) { F2P_CUDA(cudaFuncSetAttribute(project_kernel<IS_X>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024)); attr_done = true; }
+        F2P_CUDA(cudaFuncSetAttribute(project_kernel<IS_X>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
         project_kernel<IS_X><<<total_tiles, PREP_THREADS, smem, stream>>>(evecs, Cmat, pairs_dev, npairs, uniform_tiles, k, outT, ld_total, nrm, use_ft);
     }
     F2P_CUDA(cudaGetLastError());
@@ -283,8 +282,7 @@ int launch_prep(const float* ex, const float* Cmat, const float* ey, const PairD
     const size_t base = (size_t)k * (ELD + CLD) * sizeof(float);
     const int use_ft = base + (size_t)k * ELD * sizeof(float) <= 112 * 1024;   // keep 2 CTAs per SM
     const size_t smem = base + (use_ft ? (size_t)k * ELD * sizeof(float) : 0);
-    static bool attr_done = false;
-    if (!attr_done) { F2P_CUDA(cudaFuncSetAttribute(prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024)); attr_done = true; }
+    F2P_CUDA(cudaFuncSetAttribute(prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
     prep_kernel<<<total_xtiles + total_ytiles, PREP_THREADS, smem, stream>>>(ex, Cmat, ey, pairs_dev, npairs, uni_xtiles,
         total_xtiles, uni_ytiles, k, xT, ld1_total, nx, yT, ld2_total, ny, use_ft, best_init, tilecnt);
     F2P_CUDA(cudaGetLastError());

@@ -86,6 +86,7 @@ _SIGNATURES = {
     "f2p_tim_workspace_bytes": (ctypes.c_size_t, [ctypes.c_int]),
     "f2p_compute_tims": (ctypes.c_int, [_c_vp, ctypes.c_int, _c_vp, _c_vp, _c_vp]),
     "f2p_measure_fp32_peak": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), _c_vp]),
+    "f2p_test_vote_band": (ctypes.c_int, [ctypes.c_double]),
     "f2p_measure_tf32_peak": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), _c_vp]),
     "f2p_tc_last_stats": (ctypes.c_int, [ctypes.POINTER(ctypes.c_ulonglong)]),
     "f2p_test_sqrt_approx_error": (ctypes.c_int, [ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.POINTER(ctypes.c_double), _c_vp]),
@@ -145,20 +146,28 @@ _workspaces = {}
 
 
 def workspace(device, nbytes):
-    """Grow-only per-device workspace (uint8 tensor owned by torch's caching allocator)."""
-    key = (device.index if device.index is not None else torch.cuda.current_device())
-    ws = _workspaces.get(key)
-    if ws is None or ws.numel() < nbytes:
-        if ws is not None:
-            del _workspaces[key]
-            del ws
-        ws = torch.empty(int(nbytes * 1.25) + 4096, dtype=torch.uint8, device=device)
-        _workspaces[key] = ws
-    return ws
+    """Grow-only workspace per (device, current stream) — include/f2p.h forbids sharing a workspace between concurrent
+    calls on different streams, so two torch streams (or a DataLoader thread next to the main thread) get their own.
+    On growth the old buffer is handed to the caching allocator with `record_stream`, so kernels of that stream that
+    are still running keep their memory until they finish."""
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    stream = torch.cuda.current_stream(device)
+    key = (idx, stream.cuda_stream)
+    with _lock:
+        ws = _workspaces.get(key)
+        if ws is None or ws.numel() < nbytes:
+            if ws is not None:
+                ws.record_stream(stream)
+                del _workspaces[key]
+                del ws
+            ws = torch.empty(int(nbytes * 1.25) + 4096, dtype=torch.uint8, device=device)
+            _workspaces[key] = ws
+        return ws
 
 
 def release_workspaces():
-    _workspaces.clear()
+    with _lock:
+        _workspaces.clear()
 
 
 def stream_ptr(device):

@@ -32,8 +32,10 @@ def solve_sharded(solver: str, C12: Sequence[torch.Tensor], evecs_x: Sequence[to
                   evecs_y: Sequence[torch.Tensor], CAD: Optional[Sequence[torch.Tensor]] = None,
                   PC: Optional[Sequence[torch.Tensor]] = None, diam_cad: Optional[Sequence] = None,
                   group=None, compute: Optional[Callable] = None, device=None) -> List[torch.Tensor]:
-    """Every rank passes the SAME global pair list (or at least its own slice populated); each converts its slice and
-    all ranks return the full list of index maps in global pair order.
+    """Every rank passes a pair list of the SAME length; only its own slice [lo, hi) has to be populated (other entries
+    may be None).  Each rank converts its slice and all ranks return the full list of index maps in global pair order.
+    The exchange is counts first, then a payload as wide as the widest map any rank actually produced (int32 on the
+    wire) — not the 5*V2 worst case.
 
     solver: "naive" | "spatial".  `compute(solver, C, ex, ey, cad, pc, diam) -> list of [2,M]` defaults to the CUDA path.
     """
@@ -61,24 +63,28 @@ def solve_sharded(solver: str, C12: Sequence[torch.Tensor], evecs_x: Sequence[to
         device = mine[0].device if mine else (torch.device("cuda", torch.cuda.current_device())
                                               if torch.cuda.is_available() and dist.get_backend(group) == "nccl"
                                               else torch.device("cpu"))
-    # payload width: fixed by the global shapes so every rank agrees without an extra exchange
-    mult = 1 if solver == "naive" else 5
-    wmax = max([mult * int(e.shape[0]) for e in evecs_y] + [1])
-    payload, counts = pack_maps(mine, [wmax], per, device)
-    # concatenated-output form (world*per leading dim): accepted by both the NCCL and the gloo backend
-    all_payload = torch.empty((world * per,) + tuple(payload.shape[1:]), dtype=torch.int64, device=device)
+    # step 1: counts (-1 = slot not used by that rank); concatenated-output form: accepted by NCCL and gloo alike
+    counts = torch.full((per,), -1, dtype=torch.int64, device=device)
+    for i, m in enumerate(mine):
+        counts[i] = m.shape[1]
     all_counts = torch.empty((world * per,), dtype=torch.int64, device=device)
-    dist.all_gather_into_tensor(all_payload, payload, group=group)
     dist.all_gather_into_tensor(all_counts, counts, group=group)
-    all_payload = all_payload.view((world, per) + tuple(payload.shape[1:]))
-    all_counts = all_counts.view(world, per)
+    counts_host = all_counts.view(world, per).cpu()
+    # step 2: payload as wide as the widest map of ANY rank (every rank reads the same gathered counts, so they agree),
+    # int32 on the wire (indices < 2^31; row 1 may hold the reference's negative int16 wrap, which int32 keeps)
+    wmax = max(int(counts_host.max()), 1)
+    payload = torch.full((per, 2, wmax), -1, dtype=torch.int32, device=device)
+    for i, m in enumerate(mine):
+        payload[i, :, :m.shape[1]] = m.to(device=device, dtype=torch.int32)
+    all_payload = torch.empty((world * per, 2, wmax), dtype=torch.int32, device=device)
+    dist.all_gather_into_tensor(all_payload, payload, group=group)
+    all_payload = all_payload.view(world, per, 2, wmax)
     out = []
-    counts_host = all_counts.cpu()
     for r in range(world):
         for i in range(per):
             c = int(counts_host[r, i])
             if c >= 0:
-                out.append(all_payload[r, i, :, :c].contiguous())
+                out.append(all_payload[r, i, :, :c].to(torch.int64).contiguous())
     return out
 
 

@@ -20,6 +20,10 @@ def attach_results(samples: Sequence[list], p_preds: Sequence[torch.Tensor], C_p
     for b, ppp, ccc, ir in zip(samples, p_preds, C_pred, irs):
         if ppp.dtype != torch.int64 or ppp.dim() != 2 or ppp.shape[0] != 2:
             raise ValueError(f"p_pred must be int64 [2,M], got {ppp.dtype} {tuple(ppp.shape)}")
+        # the batched solvers return every p_pred as a VIEW into one batch-wide result buffer; torch.save serialises a
+        # view's whole storage, so a dense copy is attached (a few KB per file, as in the reference layout)
+        if ppp.untyped_storage().nbytes() != ppp.numel() * ppp.element_size():
+            ppp = ppp.clone()
         b[-1].update({"p_pred": ppp, "C_pred": ccc, "ir": ir})
 
 

@@ -229,6 +229,18 @@ int f2p_tc_last_stats(unsigned long long out[8]);
  * with bit patterns first_bits, first_bits + stride, ...; the error band of csrc/filter.cu assumes <= 2^-21. */
 int f2p_test_sqrt_approx_error(uint32_t first_bits, uint32_t count, uint32_t stride, double* max_rel_err, void* stream);
 
+/* Test hook (negative control of tests/test_gpu_parity.py): overrides the screened vote's error band (a fraction of the
+ * pair's extent D) for later calls of this process; band < 0 restores the proven value.  A band of 0 lets the cheap
+ * scores decide alone and CAN change the survivor set — nothing else in the library can, and no environment variable
+ * reaches it. */
+int f2p_test_vote_band(double band);
+
+/* Environment switches read by the library — all NON-semantic (every setting returns the same, exact result; they select
+ * between equivalent kernels or tilings for tests and tools/):
+ *   F2P_NN_PATH = tc | gated | exact | two_phase   kernel-2 path (default: tensor-pipe screen for large problems, gated FP32 else)
+ *   F2P_GATED_KC, F2P_GATED_NXP, F2P_NSPLIT, F2P_TOP5_MIN_TILES   tiling of the FP32 kernel-2 instances
+ *   F2P_VOTE_SCREEN = 0   ordered vote for every column;   F2P_VOTE_RB = 1 | 2 | 4   rows per basic block of the vote tile */
+
 #define F2P_STAGE_SLOTS 9
 int f2p_stage_timing(int enable);
 int f2p_stage_times(float ms[F2P_STAGE_SLOTS], double* filter_evals, double* ambiguous_cols);

@@ -10,6 +10,7 @@ oracle/ref_loader.py) is run on CPU and its outputs are stored together with a d
   <case>/diam          float64        the diam_cad actually used
   <case>/digest        str            sha256 of the inputs
   <case>/skipped       bool           whether the reference printed "skipped" (spacial_filtering.py:70-71)
+  <case>/at_risk       int32          naive: columns whose best two reference distances are within 1 ulp (census)
   <case>/ir            float32        utils.compute_inlier_ratio(p_pred.t(), CAD, aligned_pc, 0.1*diam) (utils/utils.py:81-105,
                                       as called at scripts/eval.py:88); 0 for an empty map
 """
@@ -80,6 +81,15 @@ def main():
             out[name + "/ir"] = np.float32(float(ir))
         C2 = inp["C12"].squeeze(0) if inp["C12"].dim() == 3 else inp["C12"]
         feat = torch.matmul(inp["evecs_x"], C2.t())
+        if c["kind"] == "naive" and c["n1"] * c["n2"] <= 100_000_000 and c["n1"] > 25:
+            # at-risk census: columns whose two smallest reference distances are within one ulp AFTER
+            # the reference's own square root — the only columns where a differently rounded sqrt could change the index
+            d = torch.cdist(feat, inp["evecs_y"])
+            t2 = d.topk(2, dim=0, largest=False).values if c["n1"] >= 2 else None
+            if t2 is not None:
+                b = t2.contiguous().view(torch.int32)
+                out[name + "/at_risk"] = torch.nonzero((b[1] - b[0]).abs() <= 1).flatten().to(torch.int32).numpy()
+            del d
         if c["kind"] == "spatial":
             sf = sys.modules["_f2p_reference.fmap2pointmap_solvers.spacial_filtering"]
             out[name + "/candidates"] = sf.nn_query(feat, inp["evecs_y"]).numpy()

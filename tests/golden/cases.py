@@ -27,6 +27,15 @@ CASES = {
     "naive_wrap_200x40000_k16": dict(kind="naive", n1=200, n2=40000, k=16, seed=19),
     "naive_k1_100x50": dict(kind="naive", n1=100, n2=50, k=1, seed=20),
     "naive_zero_300x100_k30": dict(kind="naive", n1=300, n2=100, k=30, seed=21, zero_rows=True),
+    # dense near-ties: the two best candidates of many columns are within an ulp after the square root
+    "naive_uniform_k1_50000x1000": dict(kind="naive", n1=50000, n2=1000, k=1, seed=41, gen="uniform"),
+    "naive_uniform_k2_50000x1000": dict(kind="naive", n1=50000, n2=1000, k=2, seed=42, gen="uniform"),
+    "naive_uniform_k3_50000x1000": dict(kind="naive", n1=50000, n2=1000, k=3, seed=43, gen="uniform"),
+    "naive_grid_k4_20000x1500": dict(kind="naive", n1=20000, n2=1500, k=4, seed=44, gen="grid"),
+    "naive_grid_k8_20000x1500": dict(kind="naive", n1=20000, n2=1500, k=8, seed=45, gen="grid"),
+    "naive_grid_k32_20000x1500": dict(kind="naive", n1=20000, n2=1500, k=32, seed=46, gen="grid"),
+    "naive_offset_k8_20000x1000": dict(kind="naive", n1=20000, n2=1000, k=8, seed=47, gen="offset"),
+    "naive_offset_k32_20000x1000": dict(kind="naive", n1=20000, n2=1000, k=32, seed=48, gen="offset"),
     # spatial-consistency solver (spacial_filtering.py:4-75)
     "spatial_300x200_k30": dict(kind="spatial", n1=300, n2=200, k=30, seed=31),
     "spatial_1000x333_k50": dict(kind="spatial", n1=1000, n2=333, k=50, seed=32),
@@ -43,6 +52,8 @@ CASES = {
 def build_inputs(name, diam_override=None):
     """Returns dict(C12, evecs_x, evecs_y, CAD, PC, diam_cad) of CPU tensors for a registered case."""
     c = CASES[name]
+    if c.get("gen"):
+        return hard_inputs(c)
     P = make_pair(c["n1"], c["n2"], c["k"], seed=c["seed"])
     C12, ex, ey, CAD, PC, diam = P.C12, P.evecs_x, P.evecs_y, P.CAD, P.PC, P.diam_cad
     if c.get("dup_rows"):
@@ -69,6 +80,29 @@ def build_inputs(name, diam_override=None):
     return dict(C12=C12, evecs_x=ex, evecs_y=ey, CAD=CAD, PC=PC, diam_cad=diam)
 
 
+def hard_inputs(c):
+    """Near-tie-dense pairs (identity functional map, so the projected features are the eigenbasis rows themselves):
+    uniform   rand(n,k) at k = 1..3 with n1 >= 50k: thousands of CAD rows per unit of distance resolution;
+    grid      randint(-4,5)/8 on a coarse lattice: exact multi-way ties in the squared distance;
+    offset    100 + 1e-2*rand: catastrophic cancellation in |x|^2 + |y|^2 - 2 x.y (many values clamp at 0)."""
+    n1, n2, k = c["n1"], c["n2"], c["k"]
+    g = torch.Generator().manual_seed(c["seed"])
+    if c["gen"] == "uniform":
+        ex, ey = torch.rand(n1, k, generator=g), torch.rand(n2, k, generator=g)
+    elif c["gen"] == "grid":
+        ex = torch.randint(-4, 5, (n1, k), generator=g).float() / 8
+        ey = torch.randint(-4, 5, (n2, k), generator=g).float() / 8
+    elif c["gen"] == "offset":
+        ex = 100.0 + 1e-2 * torch.rand(n1, k, generator=g)
+        ey = 100.0 + 1e-2 * torch.rand(n2, k, generator=g)
+    else:
+        raise ValueError(c["gen"])
+    CAD = 10.0 * torch.rand(n1, 3, generator=g)
+    PC = 10.0 * torch.rand(n2, 3, generator=g)
+    diam = float(torch.linalg.norm(CAD.max(0).values - CAD.min(0).values))
+    return dict(C12=torch.eye(k), evecs_x=ex.contiguous(), evecs_y=ey.contiguous(), CAD=CAD, PC=PC, diam_cad=diam)
+
+
 def inputs_digest(inp) -> str:
     h = hashlib.sha256()
     for key in ("C12", "evecs_x", "evecs_y", "CAD", "PC"):
@@ -82,6 +116,8 @@ def aligned_pc(name, inp):
     """The scene cloud under the ground-truth pose for the inlier-ratio cases (`Obj["align_pc"]`, scripts/eval.py:88):
     CAD[gt] plus a small seeded jitter for scene points with a ground-truth CAD vertex, the raw scene point otherwise."""
     c = CASES[name]
+    if c.get("gen"):
+        return inp["PC"].clone()
     P = make_pair(c["n1"], c["n2"], c["k"], seed=c["seed"])
     g = torch.Generator().manual_seed(c["seed"] + 777)
     n2 = c["n2"]

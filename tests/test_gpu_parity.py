@@ -2,6 +2,7 @@
 C-ABI, against the golden vectors of the real reference and against the CPU oracle on the same seeded inputs.
 Bar: bit-exact indices / masks / intermediate FP32 bits."""
 import ctypes
+import os
 
 import numpy as np
 import pytest
@@ -864,9 +865,152 @@ def test_screened_vote_band_is_what_protects_the_result(solvers, oracle, monkeyp
     PC = torch.stack([20 + 5.3 * torch.cos(ang), 30 + 5.3 * torch.sin(ang), torch.ones(M, dtype=torch.float64)], 1).float()
     p = torch.stack([torch.arange(M), torch.arange(M)], 0).contiguous()
     kept, thr = _oracle_filter_with_thresholds(oracle, CAD.numpy(), PC.numpy(), lambda s, r: np.float32(np.median(s)))
-    monkeypatch.setenv("F2P_VOTE_BAND", "0")
-    unprotected, _ = _filter_call(L, _lib, CAD, PC, p, thr)
-    monkeypatch.delenv("F2P_VOTE_BAND")
+    _lib.check(L.f2p_test_vote_band(0.0), "f2p_test_vote_band")      # the only way to change the band: an explicit call
+    try:
+        unprotected, _ = _filter_call(L, _lib, CAD, PC, p, thr)
+    finally:
+        _lib.check(L.f2p_test_vote_band(-1.0), "f2p_test_vote_band")
     protected, _ = _filter_call(L, _lib, CAD, PC, p, thr)
     np.testing.assert_array_equal(protected, p.numpy()[:, kept])
     assert unprotected.shape != protected.shape or (unprotected != protected).any()
+
+
+# ---------------------------------------------------------------------------------------------- near-ties / tensor-pipe screen
+HARD = [n for n, c in CASES.items() if c.get("gen")]
+
+
+@pytest.mark.parametrize("name", HARD)
+def test_at_risk_columns_agree_with_the_reference(solvers, golden, name, argmin_path):
+    """Census: the columns whose two smallest REFERENCE distances are within one ulp after the
+    reference's own (MKL) square root are the only ones where this build's IEEE sqrt_rn could pick another row.
+    Every one of them must carry the reference's index, on every arg-min path."""
+    c, inp = load_case(golden, name)
+    risk = golden[name + "/at_risk"]
+    d = _cuda(inp)
+    got = solvers.naive_fmap2pointmap(d["C12"], d["evecs_x"], d["evecs_y"], int16_compat=True).cpu().numpy()
+    want = golden[name + "/p_pred"]
+    np.testing.assert_array_equal(got[0][risk], want[0][risk])
+    print(f"{name}: {len(risk)} of {c['n2']} columns at risk, all equal to the reference")
+
+
+@pytest.mark.parametrize("gen,k", [("uniform", 2), ("grid", 8), ("grid", 32), ("offset", 8), ("offset", 32)])
+def test_top5_dense_near_ties_vs_oracle(solvers, oracle, gen, k, top5_path):
+    """5 nearest rows on near-tie-dense inputs through both gated paths and the tensor-pipe path: ordered by
+    (distance, index) exactly like the oracle (the reference's own order of exact ties is undefined: unstable sort)."""
+    from golden.cases import hard_inputs
+    from fmap2pointmap_solvers import _lib
+    L = _lib.load()
+    n1, n2 = 6000, 700
+    inp = hard_inputs(dict(n1=n1, n2=n2, k=k, seed=900 + k, gen=gen))
+    ex, ey, C = inp["evecs_x"], inp["evecs_y"], inp["C12"]
+    ld1, ld2 = (n1 + 127) // 128 * 128, (n2 + 127) // 128 * 128
+    xT = torch.empty(k, ld1, device="cuda"); nx = torch.empty(ld1, device="cuda")
+    yT = torch.empty(k, ld2, device="cuda"); ny = torch.empty(ld2, device="cuda")
+    ws = _ws(L.f2p_project_workspace_bytes())
+    exd, eyd, Cd = ex.cuda(), ey.cuda(), C.cuda()
+    _lib.check(L.f2p_project(exd.data_ptr(), n1, k, k, Cd.data_ptr(), xT.data_ptr(), nx.data_ptr(), ld1, ws.data_ptr(), ws.numel(), None), "f2p_project")
+    _lib.check(L.f2p_project(eyd.data_ptr(), n2, k, k, None, yT.data_ptr(), ny.data_ptr(), ld2, ws.data_ptr(), ws.numel(), None), "f2p_project")
+    wsn = _ws(L.f2p_nn_workspace_bytes(n1, n2, k, 1))
+    out = torch.empty(5 * n2, dtype=torch.int64, device="cuda")
+    _lib.check(L.f2p_nn_top5(xT.data_ptr(), nx.data_ptr(), n1, ld1, yT.data_ptr(), ny.data_ptr(), n2, ld2, k, out.data_ptr(),
+                             wsn.data_ptr(), wsn.numel(), None), "f2p_nn_top5")
+    torch.cuda.synchronize()
+    np.testing.assert_array_equal(out.cpu().numpy().reshape(n2, 5), oracle.nn_top5(oracle.project(ex, C), ey))
+
+
+def _tc_stats():
+    from fmap2pointmap_solvers import _lib
+    a = (ctypes.c_ulonglong * 8)()
+    _lib.check(_lib.load().f2p_tc_last_stats(a), "f2p_tc_last_stats")
+    return dict(recorded=a[0], overflowed=a[1], verified=a[2], violations=a[3])
+
+
+def test_tensor_pipe_screen_counters_and_lower_bound(solvers, oracle, monkeypatch):
+    """The screen's run-time self-check: every re-evaluated candidate's tensor-pipe lower bound must be <= the exact FP32
+    value (a violation would mean the error-band assumptions of csrc/tc.cu do not hold on this device), and on separated
+    data about one candidate per column survives to the exact evaluation."""
+    from fmap2pointmap_solvers.synth import make_pair
+    monkeypatch.setenv("F2P_NN_PATH", "tc")
+    for (n1, n2, k) in [(3000, 1000, 64), (2500, 700, 128), (4000, 333, 30)]:
+        P = make_pair(n1, n2, k, seed=n1 + k)
+        got = solvers.naive_fmap2pointmap(P.C12.cuda(), P.evecs_x.cuda(), P.evecs_y.cuda()).cpu().numpy()
+        np.testing.assert_array_equal(got, oracle.naive(P.C12, P.evecs_x, P.evecs_y, int16_compat=False))
+        s = _tc_stats()
+        assert s["violations"] == 0 and s["overflowed"] == 0
+        assert n2 <= s["verified"] <= 3 * n2, s
+
+
+def test_tensor_pipe_screen_falls_back_when_everything_is_in_band(solvers, golden, monkeypatch):
+    """offset inputs (100 + 1e-2*rand): every squared distance lies inside the screen's error band, the candidate lists
+    overflow, the column tiles are flagged and the FP32 kernels produce the (reference-identical) result."""
+    monkeypatch.setenv("F2P_NN_PATH", "tc")
+    name = "naive_offset_k32_20000x1000"
+    c, inp = load_case(golden, name)
+    d = _cuda(inp)
+    got = solvers.naive_fmap2pointmap(d["C12"], d["evecs_x"], d["evecs_y"], int16_compat=True).cpu().numpy()
+    np.testing.assert_array_equal(got, golden[name + "/p_pred"])
+    s = _tc_stats()
+    assert s["overflowed"] > 0 and s["violations"] == 0, s
+
+
+def test_tensor_pipe_screen_rejects_operands_outside_the_proven_range(solvers, oracle, monkeypatch):
+    """Squared norms above 2^100: the packing kernel marks the pair, the screen skips it and the FP32 kernels run."""
+    from fmap2pointmap_solvers.synth import make_pair
+    monkeypatch.setenv("F2P_NN_PATH", "tc")
+    P = make_pair(2000, 500, 32, seed=4242)
+    ex, ey = P.evecs_x * 3e16, P.evecs_y * 3e16
+    got = solvers.naive_fmap2pointmap(P.C12.cuda(), ex.cuda(), ey.cuda()).cpu().numpy()
+    np.testing.assert_array_equal(got, oracle.naive(P.C12, ex, ey, int16_compat=False))
+    s = _tc_stats()
+    assert s["recorded"] == 0 and s["verified"] == 0, s
+
+
+def test_top5_bootstrap_ties_keep_the_lowest_indices(solvers, oracle, monkeypatch):
+    """duplicated CAD rows INSIDE the first 128-row tile, at positions the gated kernel's interleaved
+    bootstrap visits out of index order (0,4,8,... before 1,5,9,...): the 5 nearest must be the (distance, index)-least
+    — e.g. rows {0,1,4,8,12}, not {0,4,8,12,16} — on the gated path as on every other."""
+    from fmap2pointmap_solvers import _lib
+    L = _lib.load()
+    n1, n2, k = 640, 130, 24
+    g = torch.Generator().manual_seed(321)
+    ex = torch.randn(n1, k, generator=g)
+    ey = 0.01 * torch.randn(n2, k, generator=g)
+    dup = [0, 4, 8, 12, 16, 1, 5, 21, 33]
+    ex[dup] = 0.001 * torch.randn(1, k, generator=g)          # nine identical rows, by far the nearest to every scene point
+    C = torch.eye(k)
+    want = oracle.nn_top5(oracle.project(ex, C), ey)
+    assert (np.sort(want, 1) == np.array([0, 1, 4, 5, 8])).all()
+    ld1, ld2 = (n1 + 127) // 128 * 128, (n2 + 127) // 128 * 128
+    for path in ("gated", "exact", "tc"):
+        monkeypatch.setenv("F2P_NN_PATH", path)
+        xT = torch.empty(k, ld1, device="cuda"); nx = torch.empty(ld1, device="cuda")
+        yT = torch.empty(k, ld2, device="cuda"); ny = torch.empty(ld2, device="cuda")
+        ws = _ws(L.f2p_project_workspace_bytes())
+        exd, eyd, Cd = ex.cuda(), ey.cuda(), C.cuda()
+        _lib.check(L.f2p_project(exd.data_ptr(), n1, k, k, Cd.data_ptr(), xT.data_ptr(), nx.data_ptr(), ld1, ws.data_ptr(), ws.numel(), None), "f2p_project")
+        _lib.check(L.f2p_project(eyd.data_ptr(), n2, k, k, None, yT.data_ptr(), ny.data_ptr(), ld2, ws.data_ptr(), ws.numel(), None), "f2p_project")
+        wsn = _ws(L.f2p_nn_workspace_bytes(n1, n2, k, 1))
+        out = torch.empty(5 * n2, dtype=torch.int64, device="cuda")
+        _lib.check(L.f2p_nn_top5(xT.data_ptr(), nx.data_ptr(), n1, ld1, yT.data_ptr(), ny.data_ptr(), n2, ld2, k, out.data_ptr(),
+                                 wsn.data_ptr(), wsn.numel(), None), "f2p_nn_top5")
+        torch.cuda.synchronize()
+        np.testing.assert_array_equal(out.cpu().numpy().reshape(n2, 5), want, err_msg=path)
+
+
+def test_saved_results_hold_only_their_own_map(solvers, tmp_path):
+    """p_pred views of the batch-wide result buffer must not drag that buffer into every .pt file."""
+    from fmap2pointmap_solvers.batched import spatial_batched
+    from fmap2pointmap_solvers.results_io import attach_results, load_results, save_results
+    from fmap2pointmap_solvers.synth import make_pair
+    Ps = [make_pair(600, 300, 30, seed=800 + i) for i in range(3)]
+    maps = spatial_batched([p.C12.cuda() for p in Ps], [p.evecs_x.cuda() for p in Ps], [p.evecs_y.cuda() for p in Ps],
+                           [p.CAD.cuda() for p in Ps], [p.PC.cuda() for p in Ps], [p.diam_cad * 3 for p in Ps], verbose=False)
+    samples = [[{"xyz": p.CAD}, {"xyz": p.PC}, {"obj_id": i}] for i, p in enumerate(Ps)]
+    attach_results(samples, maps, [p.C12 for p in Ps], [0.5] * 3)
+    paths = save_results(samples, str(tmp_path))
+    for path, m in zip(paths, maps):
+        assert os.path.getsize(path) < 200_000 + m.numel() * 8
+    for r, m in zip(load_results(str(tmp_path), map_location="cpu"), maps):
+        pp = r[-1]["p_pred"]
+        assert pp.untyped_storage().nbytes() == pp.numel() * 8
+        assert torch.equal(pp, m.cpu())

@@ -88,9 +88,15 @@ def _worker(rank, world, port, q):
 
     ok = True
     try:
+      from fmap2pointmap_solvers.distributed import shard_range
+      lo, hi = shard_range(len(Ps), world, rank)
+
+      def own(vals):      # only this rank's slice is populated: the other entries are placeholders
+          return [v if lo <= i < hi else None for i, v in enumerate(vals)]
       for kind in ("naive", "spatial"):
-        res = solve_sharded(kind, [p.C12 for p in Ps], [p.evecs_x for p in Ps], [p.evecs_y for p in Ps],
-                            [p.CAD for p in Ps], [p.PC for p in Ps], [p.diam_cad * 3 for p in Ps], compute=compute)
+        res = solve_sharded(kind, own([p.C12 for p in Ps]), own([p.evecs_x for p in Ps]), own([p.evecs_y for p in Ps]),
+                            own([p.CAD for p in Ps]), own([p.PC for p in Ps]), own([p.diam_cad * 3 for p in Ps]),
+                            compute=compute)
         want = compute(kind, [p.C12 for p in Ps], [p.evecs_x for p in Ps], [p.evecs_y for p in Ps],
                        [p.CAD for p in Ps], [p.PC for p in Ps], [p.diam_cad * 3 for p in Ps])
         ok = ok and len(res) == len(want) and all(torch.equal(a, b) for a, b in zip(res, want))
