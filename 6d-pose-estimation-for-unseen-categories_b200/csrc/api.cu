@@ -332,6 +332,23 @@ int f2p_stage_timing(int enable) {
     return 0;
 }
 
+int f2p_stage_filter_executed(double* executed_evals, double* skipped_rounds) {
+    if (!executed_evals) { set_error("null pointer"); return F2P_EINVAL; }
+    std::lock_guard<std::mutex> lk(g_stage_mu);
+    double s = 0.0, sk = 0.0;
+    for (int* p : g_stage.cnt) {
+        int c[9];
+        F2P_CUDA(cudaMemcpy(c, p, sizeof(c), cudaMemcpyDeviceToHost));
+        for (int r = 0; r < 3; ++r) {
+            if (r > 0 && c[r] == c[r - 1]) { sk += 1.0; continue; }     // predecessor pruned nothing: the vote is skipped
+            s += 0.5 * (double)c[r] * ((double)c[r] + 1.0);              // each unordered pair (and the diagonal) once
+        }
+    }
+    *executed_evals = s;
+    if (skipped_rounds) *skipped_rounds = sk;
+    return 0;
+}
+
 int f2p_stage_times(float* ms, double* filter_evals, double* ambiguous_cols) {
     if (!ms) { set_error("null pointer"); return F2P_EINVAL; }
     std::lock_guard<std::mutex> lk(g_stage_mu);

@@ -135,14 +135,20 @@ def _is_stacked(x):
 class _PackedStacked:
     """A uniform batch given as stacked tensors (C [P,k,k] or [k,k] shared, evecs_x [P,n1,k], evecs_y [P,n2,k],
     CAD [P,ncad,3], PC [P,npc,3]): one device view per operand and a vectorised descriptor fill — no per-pair Python
-    work, and CPU inputs cost one H2D copy per operand."""
+    work, and CPU inputs cost one H2D copy per operand.
+    The CAD-side operands may be SHARED by runs of consecutive pairs (many scenes of one object, the usual shape of
+    an evaluation set): evecs_x [G,n1,k] and CAD [G,ncad,3] with G dividing P serve pairs i*P/G .. (i+1)*P/G - 1; every
+    pair still has its own C, evecs_y and PC."""
 
     def __init__(self, C12, evecs_x, evecs_y, device, CAD=None, PC=None, diam_cad=None):
         import numpy as np
         ex = _lib.dev_f32(evecs_x, device).contiguous()
         ey = _lib.dev_f32(evecs_y, device).contiguous()
-        n, n1, k = (int(v) for v in ex.shape)
-        n2 = int(ey.shape[1])
+        gx, n1, k = (int(v) for v in ex.shape)
+        n, n2 = int(ey.shape[0]), int(ey.shape[1])
+        if gx < 1 or n % gx:
+            raise RuntimeError(f"stacked batch: evecs_x has {gx} entries for {n} pairs (must divide the pair count)")
+        rep_x = n // gx
         C = _lib.dev_f32(C12, device)
         if C.dim() == 2:
             C = C.unsqueeze(0)
@@ -160,7 +166,7 @@ class _PackedStacked:
         assert dt.itemsize == ctypes.sizeof(_lib.F2PPairDesc)
         d = np.zeros(max(n, 1), dt)
         i = np.arange(max(n, 1), dtype=np.int64)
-        d["evecs_x_off"] = i * (n1 * k); d["evecs_y_off"] = i * (n2 * k)
+        d["evecs_x_off"] = (i // rep_x) * (n1 * k); d["evecs_y_off"] = i * (n2 * k)
         d["c_off"] = 0 if C.shape[0] == 1 else i * (k * k)
         d["n1"], d["n2"], d["ldx"], d["ldy"] = n1, n2, k, k
         self.cad_base = self.pc_base = ex.data_ptr()
@@ -169,11 +175,11 @@ class _PackedStacked:
             pc = _lib.dev_f32(PC, device).contiguous()
             if cad.dim() == 2:
                 cad = cad.unsqueeze(0)
-            if cad.dim() != 3 or cad.shape[2] != 3 or pc.dim() != 3 or pc.shape[2] != 3 or pc.shape[0] != n or cad.shape[0] not in (1, n):
-                raise RuntimeError("stacked batch: CAD must be [P,ncad,3] (or one shared [ncad,3]) and PC [P,npc,3]")
+            if cad.dim() != 3 or cad.shape[2] != 3 or pc.dim() != 3 or pc.shape[2] != 3 or pc.shape[0] != n or cad.shape[0] < 1 or n % cad.shape[0]:
+                raise RuntimeError("stacked batch: CAD must be [P,ncad,3] (or [G,ncad,3] shared by runs of P/G pairs) and PC [P,npc,3]")
             self.keep += [cad, pc]
             self.cad_base, self.pc_base = cad.data_ptr(), pc.data_ptr()
-            d["cad_off"] = 0 if cad.shape[0] == 1 else i * (int(cad.shape[1]) * 3)
+            d["cad_off"] = (i // (n // int(cad.shape[0]))) * (int(cad.shape[1]) * 3)
             d["pc_off"] = i * (int(pc.shape[1]) * 3)
             d["ncad"], d["npc"] = int(cad.shape[1]), int(pc.shape[1])
             d["thr"] = thresholds_many(diam_cad, n)

@@ -39,14 +39,16 @@ def _pinned(tag, shape, dtype):
     return buf
 
 
-def _groups(n, chunks):
+def _groups(n, chunks, align=1):
     """Pair groups [lo, hi): `chunks` equal groups, the first one split again into a quarter and three quarters — the
-    first upload is the only one no kernel can hide, so it is kept short (a quarter of a group)."""
+    first upload is the only one no kernel can hide, so it is kept short (a quarter of a group).  Boundaries are
+    multiples of `align` (the number of consecutive pairs that share a CAD-side operand)."""
     chunks = max(1, min(int(chunks), n))
     step = (n + chunks - 1) // chunks
+    step = (step + align - 1) // align * align
     groups = [(lo, min(n, lo + step)) for lo in range(0, n, step)]
     lo, hi = groups[0]
-    head = (hi - lo) // 4
+    head = (hi - lo) // 4 // align * align
     if len(groups) > 1 and head >= 8:
         groups[0:1] = [(lo, lo + head), (lo + head, hi)]
     return groups
@@ -58,25 +60,39 @@ def _check_host(*ts):
             raise ValueError("the pipelined entry points take stacked 3-D HOST tensors ([P,n,k] ...)")
 
 
+def _share_align(n, *ops):
+    """Pairs per shared entry of the most widely shared operand (1 when every pair has its own operands)."""
+    align = 1
+    for t in ops:
+        g = int(t.shape[0])
+        if g < 1 or n % g:
+            raise ValueError(f"an operand with {g} entries cannot be shared by {n} pairs (must divide the pair count)")
+        if g > 1 or n == 1:
+            align = max(align, n // g)
+    return align
+
+
 def _device():
     if not torch.cuda.is_available():
         raise RuntimeError("fmap2pointmap_solvers (B200 build) needs a CUDA device: there is no CPU fallback")
     return torch.device("cuda", torch.cuda.current_device())
 
 
-def _sl(t, lo, hi):
-    """Group slice of a stacked operand; an operand shared by the whole batch ([1,...]) is passed whole."""
-    return t if t.shape[0] == 1 else t[lo:hi]
+def _sl(t, lo, hi, n):
+    """Pair-group slice of a stacked operand with t.shape[0] entries for n pairs (an entry serves n / t.shape[0]
+    consecutive pairs; group boundaries are aligned to that, see _groups)."""
+    rep = n // t.shape[0]
+    return t[lo // rep:(hi + rep - 1) // rep]
 
 
-def _upload(h2d, comp, device, host_ops, lo, hi, dev_ops):
+def _upload(h2d, comp, device, host_ops, lo, hi, dev_ops, n):
     with torch.cuda.stream(h2d):
         for src, dst in zip(host_ops, dev_ops):
-            if src.shape[0] == 1:
-                if lo == 0:
-                    dst.copy_(src, non_blocking=True)
-            else:
-                dst[lo:hi].copy_(src[lo:hi], non_blocking=True)
+            if src.shape[0] == 1 and lo > 0:
+                continue                      # shared by the whole batch: uploaded with the first group
+            rep = n // src.shape[0]
+            a, b = lo // rep, (hi + rep - 1) // rep
+            dst[a:b].copy_(src[a:b], non_blocking=True)
         ev = torch.cuda.Event()
         ev.record(h2d)
     comp.wait_event(ev)
@@ -88,9 +104,10 @@ def spatial_host_pipelined(C12, evecs_x, evecs_y, CAD, PC, diam_cad, chunks=4, i
     _lib.load()
     _check_host(C12 if C12.dim() == 3 else C12.reshape(-1, C12.shape[-2], C12.shape[-1]), evecs_x, evecs_y, CAD, PC)
     device = _device()
-    n, n2 = int(evecs_x.shape[0]), int(evecs_y.shape[1])
+    n, n2 = int(evecs_y.shape[0]), int(evecs_y.shape[1])
     if len(diam_cad) != n:
         raise ValueError("diam_cad must have one entry per pair")
+    align = _share_align(n, C12 if C12.dim() == 3 else C12.reshape(-1, C12.shape[-2], C12.shape[-1]), evecs_x, CAD, PC)
     flat_h = _pinned("sp_flat", (n, 10 * n2), torch.int64)
     meta_h = _pinned("sp_meta", (2, n), torch.int32)
     if n == 0:
@@ -105,9 +122,9 @@ def spatial_host_pipelined(C12, evecs_x, evecs_y, CAD, PC, diam_cad, chunks=4, i
         for t in dev_ops:
             t.record_stream(h2d)
         diam = list(diam_cad)
-        for lo, hi in _groups(n, chunks):
-            _upload(h2d, comp, device, host_ops, lo, hi, dev_ops)
-            flat, counts, status = spatial_batched(*[_sl(t, lo, hi) for t in dev_ops], diam[lo:hi], int16_compat=int16_compat,
+        for lo, hi in _groups(n, chunks, align):
+            _upload(h2d, comp, device, host_ops, lo, hi, dev_ops, n)
+            flat, counts, status = spatial_batched(*[_sl(t, lo, hi, n) for t in dev_ops], diam[lo:hi], int16_compat=int16_compat,
                                                    verbose=False, packed=True)
             ev = torch.cuda.Event()
             ev.record(comp)
@@ -131,7 +148,8 @@ def naive_host_pipelined(C12, evecs_x, evecs_y, chunks=4, int16_compat=False):
     C3 = C12 if C12.dim() == 3 else C12.reshape(-1, C12.shape[-2], C12.shape[-1])
     _check_host(C3, evecs_x, evecs_y)
     device = _device()
-    n, n2 = int(evecs_x.shape[0]), int(evecs_y.shape[1])
+    n, n2 = int(evecs_y.shape[0]), int(evecs_y.shape[1])
+    align = _share_align(n, C3, evecs_x)
     out_h = _pinned("nv", (n, 2, n2), torch.int64)
     if n == 0 or n2 == 0:
         return out_h
@@ -143,9 +161,9 @@ def naive_host_pipelined(C12, evecs_x, evecs_y, chunks=4, int16_compat=False):
         dev_ops = [torch.empty(t.shape, dtype=torch.float32, device=device) for t in host_ops]
         for t in dev_ops:
             t.record_stream(h2d)
-        for lo, hi in _groups(n, chunks):
-            _upload(h2d, comp, device, host_ops, lo, hi, dev_ops)
-            maps = naive_batched(*[_sl(t, lo, hi) for t in dev_ops], int16_compat=int16_compat)
+        for lo, hi in _groups(n, chunks, align):
+            _upload(h2d, comp, device, host_ops, lo, hi, dev_ops, n)
+            maps = naive_batched(*[_sl(t, lo, hi, n) for t in dev_ops], int16_compat=int16_compat)
             ev = torch.cuda.Event()
             ev.record(comp)
             maps.record_stream(d2h)

@@ -244,6 +244,10 @@ int f2p_test_vote_band(double band);
 #define F2P_STAGE_SLOTS 9
 int f2p_stage_timing(int enable);
 int f2p_stage_times(float ms[F2P_STAGE_SLOTS], double* filter_evals, double* ambiguous_cols);
+/* Work the vote kernels of the last timed call actually EXECUTED: sum over pairs and over the rounds that ran of
+ * M_r (M_r + 1) / 2 evaluations (each unordered pair once; a round whose predecessor pruned nothing is skipped), and the
+ * number of (pair, round) votes skipped.  Synchronous; call after f2p_stage_times. */
+int f2p_stage_filter_executed(double* executed_evals, double* skipped_rounds);
 
 #ifdef __cplusplus
 }

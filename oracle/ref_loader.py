@@ -1,7 +1,9 @@
-"""Imports the UNMODIFIED reference solvers from /root/reference (build container only).
+"""Imports the UNMODIFIED reference solvers from /root/reference (build container) or from the copy that
+`__graft_entry__.build()` stages into the git-ignored oracle/_ref/ (travels to the GPU box with the working tree).
 
-TEST INFRASTRUCTURE: used by oracle/make_golden.py and by tests that pin the C oracle against the live
-reference when /root/reference exists.  The GPU box has no /root/reference; nothing run there imports this.
+TEST / BENCH INFRASTRUCTURE: used by oracle/make_golden.py, by tests that pin the C oracle against the live
+reference, and by bench.py's CPU legs (`cpu_baseline`, `--impl reference`), which time the reference's own solvers.
+Nothing in the product path imports this.
 
 The reference package (`/root/reference/fmap2pointmap_solvers/__init__.py:1-8`) imports `gin`, which is not
 installed here; a no-op `gin.configurable` shim is injected so the reference code itself stays untouched.
@@ -11,7 +13,46 @@ import os
 import sys
 import types
 
-REFERENCE_ROOT = os.environ.get("F2P_REFERENCE_ROOT", "/root/reference")
+_HERE = os.path.dirname(os.path.abspath(__file__))
+STAGED_ROOT = os.path.join(_HERE, "_ref")
+REFERENCE_FILES = ("fmap2pointmap_solvers/__init__.py", "fmap2pointmap_solvers/naive.py",
+                   "fmap2pointmap_solvers/spacial_filtering.py")
+
+
+def _pick_root():
+    env = os.environ.get("F2P_REFERENCE_ROOT")
+    if env:
+        return env
+    if os.path.isfile("/root/reference/fmap2pointmap_solvers/naive.py"):
+        return "/root/reference"
+    return STAGED_ROOT
+
+
+REFERENCE_ROOT = _pick_root()
+
+
+def reference_root() -> str:
+    return REFERENCE_ROOT
+
+
+def stage_reference(src_root="/root/reference") -> bool:
+    """Copies the reference's solver package (3 files, 117 lines) byte for byte into oracle/_ref/ so that the GPU box —
+    which has no /root/reference — can time the reference's own code.  oracle/_ref/ is git-ignored build output, never
+    committed.  Returns False when the source tree is absent (the GPU box: the staged copy is used as it is)."""
+    import hashlib
+    import json
+    import shutil
+    if not os.path.isfile(os.path.join(src_root, REFERENCE_FILES[1])):
+        return False
+    manifest = {}
+    for rel in REFERENCE_FILES:
+        dst = os.path.join(STAGED_ROOT, rel)
+        os.makedirs(os.path.dirname(dst), exist_ok=True)
+        shutil.copyfile(os.path.join(src_root, rel), dst)
+        manifest[rel] = hashlib.sha256(open(dst, "rb").read()).hexdigest()
+    with open(os.path.join(STAGED_ROOT, "MANIFEST.json"), "w") as f:
+        json.dump({"source": src_root, "sha256": manifest}, f, indent=1)
+    return True
 
 
 def reference_available() -> bool:

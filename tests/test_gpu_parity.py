@@ -1014,3 +1014,33 @@ def test_saved_results_hold_only_their_own_map(solvers, tmp_path):
         pp = r[-1]["p_pred"]
         assert pp.untyped_storage().nbytes() == pp.numel() * 8
         assert torch.equal(pp, m.cpu())
+
+
+def test_shared_cad_side_operands_match_per_pair_operands(solvers, oracle):
+    """Runs of consecutive pairs sharing evecs_x / CAD ([G,n1,k] for P pairs, SURVEY 8(d): one CAD per 16 scenes): same
+    maps as the batch with every pair's operands spelled out, on the device and through the host pipeline."""
+    from fmap2pointmap_solvers.batched import naive_batched, spatial_batched
+    from fmap2pointmap_solvers.pipeline import naive_host_pipelined, spatial_host_pipelined
+    from fmap2pointmap_solvers.synth import make_pair
+    G, rep, n1, n2, k = 3, 8, 700, 260, 30
+    objs = [make_pair(n1, n2, k, seed=600 + g) for g in range(G)]
+    gen = torch.Generator().manual_seed(7)
+    ex = torch.stack([o.evecs_x for o in objs]); cad = torch.stack([o.CAD for o in objs])
+    P = G * rep
+    C = torch.stack([torch.linalg.qr(torch.randn(k, k, generator=gen)).Q for _ in range(P)])
+    ey = torch.stack([objs[i // rep].evecs_y + 0.002 * torch.randn(n2, k, generator=gen) for i in range(P)])
+    pc = torch.stack([objs[i // rep].PC + 0.05 * torch.randn(n2, 3, generator=gen) for i in range(P)])
+    diam = [objs[i // rep].diam_cad * 3 for i in range(P)]
+    full_ex, full_cad = ex.repeat_interleave(rep, 0), cad.repeat_interleave(rep, 0)
+    want_n = naive_batched(C.cuda(), full_ex.cuda(), ey.cuda()).cpu()
+    got_n = naive_batched(C.cuda(), ex.cuda(), ey.cuda()).cpu()
+    assert torch.equal(got_n, want_n)
+    np.testing.assert_array_equal(got_n[5].numpy(), oracle.naive(C[5], full_ex[5], ey[5], int16_compat=False))
+    assert torch.equal(naive_host_pipelined(C, ex, ey, chunks=3), want_n)
+    want_s = spatial_batched(C.cuda(), full_ex.cuda(), ey.cuda(), full_cad.cuda(), pc.cuda(), diam, verbose=False)
+    got_s = spatial_batched(C.cuda(), ex.cuda(), ey.cuda(), cad.cuda(), pc.cuda(), diam, verbose=False)
+    assert len(got_s) == P and all(torch.equal(a, b) for a, b in zip(got_s, want_s))
+    flat, counts, status = spatial_host_pipelined(C, ex, ey, cad, pc, diam, chunks=3)
+    for i in range(P):
+        m = int(counts[i])
+        assert torch.equal(flat[i, :2 * m].view(2, m), want_s[i].cpu())
