@@ -194,16 +194,73 @@ class _PackedStacked:
         self.out_total = n * size
 
 
+# ---- single pair: the reference's real call shape (scripts/eval.py:87, one sample per loop iteration) -----------------
+# No lists, no descriptor arrays: one cached ctypes descriptor and workspace size per shape, each operand is its own base.
+_single_desc = {}
+
+
+def _single_entry(lib, spatial, n1, n2, k, ldx, ldy, ncad, npc):
+    key = (spatial, n1, n2, k, ldx, ldy, ncad, npc)
+    ent = _single_desc.get(key)
+    if ent is None:
+        d = _lib.F2PPairDesc()
+        d.n1, d.n2, d.ldx, d.ldy, d.ncad, d.npc = n1, n2, ldx, ldy, ncad, npc
+        nbytes = lib.f2p_workspace_bytes(ctypes.byref(d), 1, k, spatial)
+        if len(_single_desc) > 256:
+            _single_desc.clear()
+        ent = _single_desc[key] = (d, nbytes)
+    return ent
+
+
+def _single_operands(C12, evecs_x, evecs_y, device):
+    C = _lib.dev_f32(_squeeze_c(C12), device).contiguous()
+    ex = _lib.rowmajor_2d(_lib.dev_f32(evecs_x, device))
+    ey = _lib.rowmajor_2d(_lib.dev_f32(evecs_y, device))
+    k = int(C.shape[0])
+    if ex.shape[1] != k or ey.shape[1] != k:
+        raise RuntimeError(f"pair 0: shapes {tuple(ex.shape)} @ {tuple(C.shape)}^T vs {tuple(ey.shape)} "
+                           f"are inconsistent (all pairs of a batch must share K={k})")
+    return C, ex, ey, k
+
+
+def naive_single(C12, evecs_x, evecs_y, int16_compat=False):
+    """`naive_fmap2pointmap` for ONE pair: int64 [2,V2] on the device of `evecs_x`."""
+    lib = _lib.load()
+    device = _lib.cuda_device_for(evecs_x, evecs_y, C12)
+    with torch.cuda.device(device):
+        C, ex, ey, k = _single_operands(C12, evecs_x, evecs_y, device)
+        n1, n2 = int(ex.shape[0]), int(ey.shape[0])
+        if n1 < 1:
+            raise RuntimeError("pair 0: evecs_x has no rows (argmin of an empty dimension)")
+        out = torch.empty((2, n2), dtype=torch.int64, device=device)
+        if n2 > 0:
+            d, nbytes = _single_entry(lib, 0, n1, n2, k, int(ex.stride(0)) if n1 > 1 else k,
+                                      int(ey.stride(0)) if n2 > 1 else k, n1, n2)
+            if nbytes == 0:
+                _lib.check(-1 if k <= _lib.F2P_MAX_K else -3, "f2p_workspace_bytes")
+            ws = _lib.workspace(device, nbytes)
+            rc = lib.f2p_naive_batched(ex.data_ptr(), ey.data_ptr(), C.data_ptr(), ctypes.byref(d), 1, k,
+                                       _lib.F2P_INT16_COMPAT if int16_compat else 0, out.data_ptr(), ws.data_ptr(),
+                                       ws.numel(), _lib.stream_ptr(device))
+            _lib.check(rc, "f2p_naive_batched")
+        return out if evecs_x.is_cuda else out.to(evecs_x.device)
+
+
 def naive_batched(C12: Sequence[torch.Tensor], evecs_x: Sequence[torch.Tensor], evecs_y: Sequence[torch.Tensor],
                   int16_compat: bool = False) -> List[torch.Tensor]:
     """`naive_fmap2pointmap` (naive.py:5-21) for a list of pairs sharing K: one int64 [2,V2] tensor per pair, on the
     device of that pair's `evecs_x` (CPU inputs are copied to the current CUDA device and the result copied back)."""
     lib = _lib.load()
     if _is_stacked(evecs_x):
+        if evecs_x.shape[0] == 1 and evecs_y.shape[0] == 1 and C12.dim() in (2, 3):
+            C1 = C12 if C12.dim() == 2 else C12[0]
+            return naive_single(C1, evecs_x[0], evecs_y[0], int16_compat).unsqueeze(0)
         return _naive_stacked(lib, C12, evecs_x, evecs_y, int16_compat)
     n = len(evecs_x)
     if n == 0:
         return []
+    if n == 1 and len(C12) == 1 and len(evecs_y) == 1:
+        return [naive_single(C12[0], evecs_x[0], evecs_y[0], int16_compat)]
     device = _lib.cuda_device_for(*evecs_x, *evecs_y, *C12)
     with torch.cuda.device(device):
         pk = _Packed(C12, evecs_x, evecs_y, device)

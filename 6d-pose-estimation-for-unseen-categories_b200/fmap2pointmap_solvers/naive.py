@@ -2,7 +2,7 @@
 import torch
 
 from ._gin import configurable
-from .batched import naive_batched
+from .batched import naive_batched, naive_single
 
 
 @configurable
@@ -20,7 +20,7 @@ def naive_fmap2pointmap(C12, evecs_x, evecs_y, **kwargs):
         int64 [2, V2] on the device of `evecs_x`: row 0 = nearest shape-x vertex of every shape-y point in the
         spectral embedding (lowest index on exact distance ties), row 1 = the shape-y point index.
     """
-    return naive_batched([C12], [evecs_x], [evecs_y], int16_compat=bool(kwargs.get("int16_compat", False)))[0]
+    return naive_single(C12, evecs_x, evecs_y, int16_compat=bool(kwargs.get("int16_compat", False)))
 
 
 def nn_query(feat_x, feat_y, dim=-2):
