@@ -322,7 +322,7 @@ def measure_workload(ctx, name, wl, ppg, steps, warmup, e2e_steps):
             return spatial_batched(devt["C"], devt["ex"], devt["ey"], devt["cad"], devt["pc"], diam, verbose=False, packed=True)
         return naive_batched(devt["C"], devt["ex"], devt["ey"])
 
-    gather_ms = [0.0]
+    gbuf = {}
 
     def gather_maps(out):
         """Index maps to every rank.  naive: int32 on the wire, on the side stream (overlaps the next step's kernels).
@@ -334,14 +334,19 @@ def measure_workload(ctx, name, wl, ppg, steps, warmup, e2e_steps):
             from fmap2pointmap_solvers.distributed import allgather_packed_maps
             return allgather_packed_maps(out[0], out[1])
         comp = torch.cuda.current_stream(dev)
-        wire = out.to(torch.int32)
+        key = tuple(out.shape)
+        if key not in gbuf:       # wire / gathered / widened buffers are allocated once per workload, not per step
+            gbuf[key] = (torch.empty(key, dtype=torch.int32, device=dev),
+                         torch.empty((world,) + key, dtype=torch.int32, device=dev),
+                         torch.empty((world,) + key, dtype=torch.int64, device=dev))
+        wire, allm, res = gbuf[key]
+        comp.wait_stream(ctx.comm)            # the previous step's gather has finished with the buffers
+        wire.copy_(out)
         ev = torch.cuda.Event(); ev.record(comp)
-        wire.record_stream(ctx.comm)
         with torch.cuda.stream(ctx.comm):
             ctx.comm.wait_event(ev)
-            allm = torch.empty((world,) + tuple(wire.shape), dtype=torch.int32, device=dev)
             dist.all_gather_into_tensor(allm, wire)
-            res = allm.to(torch.int64)
+            res.copy_(allm)
         return res
 
     d2h_bytes = [0]
