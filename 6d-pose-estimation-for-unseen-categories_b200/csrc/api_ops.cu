@@ -142,6 +142,10 @@ int f2p_test_vote_band(double band) { set_vote_band_override(band); return 0; }
 
 int f2p_measure_tf32_peak(double* tflops, void* stream) { return measure_tf32_peak(tflops, static_cast<cudaStream_t>(stream)); }
 
+int f2p_measure_tmem_ld(double* bytes_per_clk_sm, double* gbs, void* stream) {
+    return measure_tmem_ld(bytes_per_clk_sm, gbs, static_cast<cudaStream_t>(stream));
+}
+
 int f2p_tc_last_stats(unsigned long long out[8]) {
     if (!out) { set_error("null pointer"); return F2P_EINVAL; }
     return tc_last_stats(out);

@@ -116,6 +116,7 @@ bool tc_enabled(double flops, int k, int top5);
 bool tc_fits(int k, int top5);   // the resident scene tile + a >= 2-deep ring fit one SM's shared memory
 int measure_tf32_peak(double* tflops, cudaStream_t st);
 int tc_last_stats(unsigned long long out[8]);
+int measure_tmem_ld(double* bytes_per_clk_sm, double* gbs, cudaStream_t st);
 
 // filter.cu
 size_t filter_pair_bytes(int M);

@@ -694,6 +694,55 @@ __global__ void __launch_bounds__(128, 1) tc_peak_kernel(int iters, float* sink)
     if (warp == 1) { tc_fence_after(); tmem_free512(tmem_base); }
 }
 
+// TMEM -> register bandwidth (tcgen05.ld 32x32b.x32) with 8 warps per SM and no MMA running: the rate that bounds the
+// screen's epilogue (every accumulator element is read once).
+__global__ void __launch_bounds__(256, 1) tc_ldtm_kernel(int iters, float* sink) {
+    __shared__ uint32_t s_tmem;
+    const int warp = threadIdx.x >> 5;
+    if (warp == 0) tmem_alloc512(&s_tmem);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t base = s_tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((warp >> 2) * 256);
+    float acc = 0.f;
+    for (int it = 0; it < iters; ++it) {
+        float v[32];
+        tmem_ld32(base + (uint32_t)((it & 7) * 32), v);
+        tmem_ld_wait();
+        acc += v[0] + v[31];
+    }
+    if (sink && acc == 123.456f) sink[threadIdx.x] = acc;
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) { tc_fence_after(); tmem_free512(s_tmem); }
+}
+
+int measure_tmem_ld(double* bytes_per_clk_sm, double* gbs, cudaStream_t st) {
+    int dev = 0, sm = 0, khz = 0;
+    F2P_CUDA(cudaGetDevice(&dev));
+    F2P_CUDA(cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev));
+    F2P_CUDA(cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev));
+    F2P_CUDA(cudaFuncSetAttribute(tc_ldtm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024));
+    cudaEvent_t e0, e1;
+    F2P_CUDA(cudaEventCreate(&e0)); F2P_CUDA(cudaEventCreate(&e1));
+    const int iters = 20000;
+    double best = 0.0;
+    for (int rep = 0; rep < 3; ++rep) {
+        F2P_CUDA(cudaEventRecord(e0, st));
+        tc_ldtm_kernel<<<sm, 256, 120 * 1024, st>>>(iters, nullptr);
+        F2P_CUDA(cudaEventRecord(e1, st));
+        F2P_CUDA(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        F2P_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        const double bps = 8.0 * 4096.0 * iters * sm / (ms * 1e-3);      // 8 warps x 4 KB per load
+        if (bps > best) best = bps;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (gbs) *gbs = best / 1e9;
+    if (bytes_per_clk_sm) *bytes_per_clk_sm = best / sm / (khz * 1e3);
+    return 0;
+}
+
 int measure_tf32_peak(double* tflops, cudaStream_t st) {
     int dev = 0, sm = 0;
     F2P_CUDA(cudaGetDevice(&dev));

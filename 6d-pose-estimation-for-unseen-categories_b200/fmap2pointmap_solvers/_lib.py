@@ -88,6 +88,7 @@ _SIGNATURES = {
     "f2p_measure_fp32_peak": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), _c_vp]),
     "f2p_test_vote_band": (ctypes.c_int, [ctypes.c_double]),
     "f2p_measure_tf32_peak": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), _c_vp]),
+    "f2p_measure_tmem_ld": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), _c_vp]),
     "f2p_tc_last_stats": (ctypes.c_int, [ctypes.POINTER(ctypes.c_ulonglong)]),
     "f2p_test_sqrt_approx_error": (ctypes.c_int, [ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.POINTER(ctypes.c_double), _c_vp]),
     "f2p_stage_timing": (ctypes.c_int, [ctypes.c_int]),

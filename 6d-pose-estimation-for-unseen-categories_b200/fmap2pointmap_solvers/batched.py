@@ -3,6 +3,7 @@
 (`scripts/eval.py:83-91`) becomes one launch sequence over all pairs; single-pair solver calls are batches of one.
 """
 import ctypes
+import os
 from typing import List, Optional, Sequence
 
 import torch
@@ -200,7 +201,8 @@ _single_desc = {}
 
 
 def _single_entry(lib, spatial, n1, n2, k, ldx, ldy, ncad, npc):
-    key = (spatial, n1, n2, k, ldx, ldy, ncad, npc)
+    # the workspace size depends on the kernel-2 path the library will pick (F2P_NN_PATH, include/f2p.h)
+    key = (spatial, n1, n2, k, ldx, ldy, ncad, npc, os.environ.get("F2P_NN_PATH"))
     ent = _single_desc.get(key)
     if ent is None:
         d = _lib.F2PPairDesc()

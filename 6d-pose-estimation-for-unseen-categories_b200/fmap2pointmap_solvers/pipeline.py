@@ -85,7 +85,9 @@ def _sl(t, lo, hi, n):
     return t[lo // rep:(hi + rep - 1) // rep]
 
 
-def _upload(h2d, comp, device, host_ops, lo, hi, dev_ops, n):
+def _upload(h2d, comp, device, host_ops, lo, hi, dev_ops, n, wait=True):
+    """Enqueues the H2D copies of pair group [lo, hi) on the copy stream; returns the event that marks their end (and
+    makes the compute stream wait for it unless wait=False)."""
     with torch.cuda.stream(h2d):
         for src, dst in zip(host_ops, dev_ops):
             if src.shape[0] == 1 and lo > 0:
@@ -95,12 +97,15 @@ def _upload(h2d, comp, device, host_ops, lo, hi, dev_ops, n):
             dst[a:b].copy_(src[a:b], non_blocking=True)
         ev = torch.cuda.Event()
         ev.record(h2d)
-    comp.wait_event(ev)
+    if wait:
+        comp.wait_event(ev)
+    return ev
 
 
-def spatial_host_pipelined(C12, evecs_x, evecs_y, CAD, PC, diam_cad, chunks=4, int16_compat=True):
+def spatial_host_pipelined(C12, evecs_x, evecs_y, CAD, PC, diam_cad, chunks=4, int16_compat=True, prefix_only=True):
     """(flat int64 [P, 2*5*V2], counts int32 [P], status int32 [P]) as pinned HOST tensors; pair i's dense [2,M'_i] map
-    is `flat[i, :2*counts[i]].view(2, -1)` (the layout of `spatial_batched(..., packed=True)`)."""
+    is `flat[i, :2*counts[i]].view(2, -1)` (the layout of `spatial_batched(..., packed=True)`).  Only those prefixes are
+    copied back: the slots behind them are unspecified."""
     _lib.load()
     _check_host(C12 if C12.dim() == 3 else C12.reshape(-1, C12.shape[-2], C12.shape[-1]), evecs_x, evecs_y, CAD, PC)
     device = _device()
@@ -122,8 +127,27 @@ def spatial_host_pipelined(C12, evecs_x, evecs_y, CAD, PC, diam_cad, chunks=4, i
         for t in dev_ops:
             t.record_stream(h2d)
         diam = list(diam_cad)
-        for lo, hi in _groups(n, chunks, align):
-            _upload(h2d, comp, device, host_ops, lo, hi, dev_ops, n)
+        pending = []        # (lo, hi, flat, event after the group's counts reached the host), oldest first
+
+        def drain(p):
+            # the result buffer is sized for the worst case (10*V2 slots per pair) and nearly empty behind the dense
+            # [2,M'] prefixes: once the group's counts are on the host, only the first 2*max(M') slots are copied back
+            plo, phi, pflat, pev = p
+            if prefix_only:
+                pev.synchronize()
+                width = min(int(pflat.shape[1]), 2 * int(meta_h[0, plo:phi].max())) if phi > plo else 0
+            else:
+                width = int(pflat.shape[1])
+            if width > 0:
+                with torch.cuda.stream(d2h):
+                    flat_h[plo:phi, :width].copy_(pflat[:, :width], non_blocking=True)
+
+        groups = _groups(n, chunks, align)
+        # every group's upload is queued up front (the copy stream runs them back to back); the host may then block on a
+        # group's survivor counts without delaying any upload
+        up = [_upload(h2d, comp, device, host_ops, lo, hi, dev_ops, n, wait=False) for lo, hi in groups]
+        for gi, (lo, hi) in enumerate(groups):
+            comp.wait_event(up[gi])
             flat, counts, status = spatial_batched(*[_sl(t, lo, hi, n) for t in dev_ops], diam[lo:hi], int16_compat=int16_compat,
                                                    verbose=False, packed=True)
             ev = torch.cuda.Event()
@@ -132,9 +156,17 @@ def spatial_host_pipelined(C12, evecs_x, evecs_y, CAD, PC, diam_cad, chunks=4, i
                 t.record_stream(d2h)
             with torch.cuda.stream(d2h):
                 d2h.wait_event(ev)
-                flat_h[lo:hi].copy_(flat, non_blocking=True)
                 meta_h[0, lo:hi].copy_(counts, non_blocking=True)
                 meta_h[1, lo:hi].copy_(status, non_blocking=True)
+                cev = torch.cuda.Event()
+                cev.record(d2h)
+            # maps are fetched two groups behind: that group's counts are on the host by now (the group in between is
+            # still running), so the host does not block while there is work left to queue
+            pending.append((lo, hi, flat, cev))
+            if len(pending) > 2:
+                drain(pending.pop(0))
+        for p in pending:
+            drain(p)
         d2h.synchronize()
     if bool((meta_h[1] & 2).any()):
         bad = int((meta_h[1] & 2).nonzero()[0][0])

@@ -357,7 +357,7 @@ def measure_workload(ctx, name, wl, ppg, steps, warmup, e2e_steps):
         if ppg > 1:
             if spatial:
                 flat, counts, status = spatial_host_pipelined(host["C"], host["ex"], host["ey"], host["cad"], host["pc"], diam)
-                d2h_bytes[0] = flat.numel() * 8 + counts.numel() * 8
+                d2h_bytes[0] = int(2 * counts.max()) * 8 * flat.shape[0] + counts.numel() * 8   # upper bound: prefix width of the widest group
                 return flat
             res = naive_host_pipelined(host["C"], host["ex"], host["ey"])
             d2h_bytes[0] = res.numel() * 8

@@ -210,6 +210,10 @@ int f2p_measure_fp32_peak(double* tflops_packed, double* tflops_scalar, void* st
  * kind::tf32, M128 N256 K8, operands in shared memory): TFLOP/s, the roofline denominator of csrc/tc.cu. */
 int f2p_measure_tf32_peak(double* tflops, void* stream);
 
+/* Measured TMEM -> register bandwidth (tcgen05.ld 32x32b.x32, 8 warps per SM, no MMA running): bytes per clock and SM at
+ * the nominal SM clock, and GB/s for the device.  Bounds the screen's epilogue (csrc/tc.cu); measurement aid. */
+int f2p_measure_tmem_ld(double* bytes_per_clk_sm, double* gbs, void* stream);
+
 /* Counters of the most recent tensor-pipe screen (synchronous read; measurement aid, no reference counterpart):
  * out[0] candidates recorded by the screen, out[1] candidate lists that overflowed (their column tiles were redone by the
  * FP32 kernels), out[2] candidates re-evaluated exactly, out[3] re-evaluated candidates whose tensor-pipe lower bound

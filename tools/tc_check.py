@@ -63,6 +63,9 @@ if __name__ == "__main__":
     pk = ctypes.c_double()
     _lib.check(L.f2p_measure_tf32_peak(ctypes.byref(pk), st), "peak")
     print(f"tf32 tensor-pipe peak (M128 N256 K8, smem operands): {pk.value:.1f} TFLOP/s", flush=True)
+    bpc, gbs = ctypes.c_double(), ctypes.c_double()
+    _lib.check(L.f2p_measure_tmem_ld(ctypes.byref(bpc), ctypes.byref(gbs), st), "tmem")
+    print(f"TMEM -> register (tcgen05.ld 32x32b.x32, 8 warps/SM): {bpc.value:.1f} B/clk/SM at the nominal clock, {gbs.value:.0f} GB/s", flush=True)
     a = [int(v) for v in sys.argv[1:]]
     shapes = [tuple(a[i:i + 4]) for i in range(0, len(a), 4)] or [
         (256, 128, 26, 0), (1000, 300, 30, 0), (5000, 2000, 50, 0), (5000, 2000, 50, 1), (10000, 4000, 128, 0),
