@@ -126,6 +126,67 @@ int f2p_nn_top5(const float* xT, const float* nx, int n1, int ld1, const float* 
     return nn_common(1, xT, nx, n1, ld1, yT, ny, n2, ld2, k, idx5_out, ws, ws_bytes, stream);
 }
 
+// ---- allocation-free arg-min (no counterpart in the reference) -----------
+// For callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): the
+// scratch of kernel 2 (merge keys, re-check buffers, the pair record) lives in ONE file-scope device array instead of a
+// caller-provided workspace.  Every GPU that loads the library holds these 2.25 MB until exit.  All calls share the
+// array and it keeps the last call's contents: the launch sequence re-initialises everything it reads (argmin_init_kernel
+// resets the merge keys / counters of the n2 columns in use), and calls that overlap on the GPU (two streams, two
+// threads) RACE on it — serialise them.
+constexpr size_t F2P_STATIC_SCRATCH_BYTES = 2304 * 1024;      // >= 256 + argmin_ws_bytes(4096, 128, 1) = 2 212 608
+static __device__ __align__(256) unsigned char g_static_scratch[F2P_STATIC_SCRATCH_BYTES];
+
+// In host code `g_static_scratch` is only a stand-in for the symbol, NOT a device address: the address is looked up
+// once per device (with that device current) and cached.
+static int static_scratch_ptr(unsigned char** out) {
+    static unsigned char* cache[64] = {nullptr};
+    static std::mutex mu;
+    int dev = 0;
+    F2P_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) { set_error("device index %d out of range", dev); return F2P_EDEVICE; }
+    std::lock_guard<std::mutex> lk(mu);
+    if (!cache[dev]) {
+        void* p = nullptr;
+        F2P_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+        if (!p) { set_error("cudaGetSymbolAddress returned a null address"); return F2P_EDEVICE; }
+        cache[dev] = static_cast<unsigned char*>(p);
+    }
+    *out = cache[dev];
+    return 0;
+}
+
+int f2p_nn_argmin_static(const float* xT, const float* nx, int n1, int ld1, const float* yT, const float* ny, int n2,
+                         int ld2, int k, int64_t* idx_out, void* stream) {
+    if (!xT || !nx || !yT || !ny || !idx_out) { set_error("null pointer"); return F2P_EINVAL; }
+    if (k < 1 || n1 < 1 || n2 < 0) { set_error("bad shape n1=%d n2=%d k=%d", n1, n2, k); return F2P_EINVAL; }
+    if (n2 > F2P_STATIC_MAX_N2 || k > F2P_STATIC_MAX_K) {
+        set_error("f2p_nn_argmin_static: n2=%d k=%d exceed the static scratch (n2 <= %d, k <= %d); use f2p_nn_argmin "
+                  "with a caller-provided workspace", n2, k, F2P_STATIC_MAX_N2, F2P_STATIC_MAX_K);
+        return F2P_ENOTSUP;
+    }
+    if (n2 == 0) return 0;
+    PairDev p;
+    const int nrt = (n1 + TILE - 1) / TILE, nct = (n2 + TILE - 1) / TILE;
+    int rc = single_pair(p, n1, n2, ld1, ld2, pick_nsplit(nrt, nct));
+    if (rc) return rc;
+    if (ld2 != nct * TILE) { set_error("f2p_nn_argmin_static needs ld2 == round_up(n2, %d)", TILE); return F2P_EINVAL; }
+    if (256 + argmin_ws_bytes(ld2, k, 1) > F2P_STATIC_SCRATCH_BYTES) {      // cannot happen within the limits above
+        set_error("f2p_nn_argmin_static: scratch of %zu bytes exceeds the static array", 256 + argmin_ws_bytes(ld2, k, 1));
+        return F2P_ENOSPACE;
+    }
+    unsigned char* ws = nullptr;
+    if ((rc = static_scratch_ptr(&ws))) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    F2P_CUDA(cudaMemcpyAsync(ws, &p, sizeof(p), cudaMemcpyHostToDevice, st));
+    const int items = p.nct * p.nsplit;
+    ArgminWs aw;
+    argmin_ws_carve(aw, ws + 256, ld2, k, 1);
+    // always the FP32 kernels (the tensor-pipe screen needs a workspace that grows with n1); pre_init = false: the
+    // sequence starts with argmin_init_kernel, so nothing of an earlier call is read
+    return launch_argmin(xT, ld1, nx, yT, ld2, ny, k, reinterpret_cast<const PairDev*>(ws), 1, items, items, p.nct, p.nct,
+                         2.0 * n1 * (double)n2 * k, F2P_ROW0_ONLY, idx_out, aw, st, false, nullptr);
+}
+
 size_t f2p_filter_workspace_bytes(int M) { return 256 + filter_pair_bytes(M < 0 ? 0 : M); }
 
 int f2p_spatial_filter(const float* cad, int ncad, const float* pc, int npc, const int64_t* p, int M,

@@ -114,6 +114,20 @@ int f2p_spatial_filter(const float* cad_dev, int ncad, const float* pc_dev, int 
                        uint8_t* mask_dev, float* scores_dev,
                        void* ws_dev, size_t ws_bytes, void* stream);
 
+/* Kernel 2 without a workspace argument and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same result as f2p_nn_argmin (the FP32 kernels; idx_out[j] int64, lowest i on exact ties).
+ * The scratch is a static device array inside the library (2.25 MB held by every GPU that loads it, until exit), which
+ * limits the shape: n2 <= F2P_STATIC_MAX_N2, k <= F2P_STATIC_MAX_K (n1 is not limited); beyond that the call returns
+ * F2P_ENOTSUP.  ld2 must equal round_up(n2, 128).  The function calls no cudaMalloc / cudaFree or allocating routine.
+ * ALL calls share the one array, which keeps the last call's contents (every call re-initialises what it reads): calls
+ * that overlap on the GPU — different streams or threads — race; serialise them. */
+#define F2P_STATIC_MAX_N2 4096
+#define F2P_STATIC_MAX_K  128
+int f2p_nn_argmin_static(const float* xT_dev, const float* nx_dev, int n1, int ld1,
+                         const float* yT_dev, const float* ny_dev, int n2, int ld2, int k,
+                         int64_t* idx_out_dev, void* stream);
+
 size_t f2p_project_workspace_bytes(void);
 size_t f2p_nn_workspace_bytes(int n1, int n2, int k, int top5);
 size_t f2p_filter_workspace_bytes(int M);
