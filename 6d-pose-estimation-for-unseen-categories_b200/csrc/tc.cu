@@ -482,74 +482,148 @@ struct TCVerifyParams {
     unsigned long long* stats;
 };
 
+// Block = one column tile (128 scene points).  The candidates of a tile are spread very unevenly over its columns (about
+// one per column on average, a dozen for a few), and one exact evaluation is a dependent chain of k FMAs fed by a cold
+// 4k-byte row: a thread per column made the whole launch wait for its unluckiest thread (ncu: 223 us at cfg4, 49
+// long-scoreboard stalls per issue).  So the tile's (column, row) items are flattened into one shared list and dealt out
+// to all 128 threads; the scene columns are staged in shared memory once, the CAD rows are L2-prefetched and read as
+// float4.  Arithmetic per item is unchanged (sequential-k fmaf, + nx, + ny, clamp, sqrt_rn).
+constexpr int VCAP = 1024;      // items per pass (a tile with more takes several passes)
+
 template <int K>
 __global__ void __launch_bounds__(TILE)
 nn_tc_verify_kernel(const TCVerifyParams prm) {
+    extern __shared__ __align__(16) float s_y[];       // [k][TILE] scene columns of this tile
+    __shared__ uint32_t s_row[VCAP];
+    __shared__ float s_lb[VCAP];
+    __shared__ u64 s_key[VCAP];
+    __shared__ uint16_t s_col[VCAP];
+    __shared__ u64 s_best[TILE];
+    __shared__ float s_ny[TILE];
+    __shared__ int s_wsum[TILE / 32];
     const int pi = find_pair(blockIdx.x, prm.pairs, prm.npairs, prm.uniform_ytiles, &PairDev::ytile0);
     const PairDev* pd = prm.pairs + pi;
     const int ct = blockIdx.x - pd->ytile0;
-    if (prm.tcflag[blockIdx.x]) return;         // redone by the FFMA2 kernels
-    const int tid = threadIdx.x;
+    if (prm.tcflag[blockIdx.x]) return;         // redone by the FFMA2 kernels (uniform exit)
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int j = ct * TILE + tid, n2 = pd->n2;
-    if (j >= n2) return;
-    const int64_t yc = (int64_t)pd->y_col0 + j;
-    const uint32_t tau = prm.tau[yc];
-    const float nyj = prm.ny[yc];
+    const int64_t yc = (int64_t)pd->y_col0 + j;   // padded columns exist in yT / ny / tau / ccnt (all zero / empty)
     const int k = prm.k;
-    const float* yp = prm.yT + yc;
-    u64 best[K];
-#pragma unroll
-    for (int r = 0; r < K; ++r) best[r] = ~0ull;
-    unsigned long long nver = 0, nviol = 0;
+    const uint32_t tau = prm.tau[yc];
+    s_ny[tid] = prm.ny[yc];
+    s_best[tid] = ~0ull;
+    {   // stage the tile's scene columns: k independent coalesced loads per thread
+        const float* yp = prm.yT + yc;
+#pragma unroll 8
+        for (int c = 0; c < k; ++c) s_y[c * TILE + tid] = __ldg(yp + (int64_t)c * prm.ld2_total);
+    }
     const int nsplit = pd->tc_nsplit;
-    for (int sh = 0; sh < nsplit * prm.eh; ++sh) {
+    const int nlists = nsplit * prm.eh;
+    auto list_of = [&](int sh, const u64*& cl) -> int {
         // lists of the CTA (item, cluster rank) that screened this column tile for row split sh / eh, accumulator half sh % eh
         const size_t item = (size_t)pd->tc_item0 + (size_t)(ct / TC_CG) * nsplit + (size_t)(sh / prm.eh);
         const size_t slot = (item * TC_CG + (size_t)(ct % TC_CG)) * prm.eh + (size_t)(sh % prm.eh);
-        const int n = prm.ccnt[slot * TILE + tid];
-        const u64* cl = prm.cand + slot * prm.cap * TILE + tid;
-        for (int e = 0; e < n; ++e) {
-            const u64 ce = cl[(size_t)e * TILE];
-            if ((uint32_t)(ce >> 32) >= tau) continue;            // LB >= final threshold: cannot be among the K best
-            const uint32_t i = (uint32_t)(ce & 0xffffffffull);
-            const float* xp = prm.XR + ((int64_t)pd->xa_row0 + i) * k;      // 4k contiguous bytes: a few cache lines
+        cl = prm.cand + slot * prm.cap * TILE + tid;
+        return prm.ccnt[slot * TILE + tid];
+    };
+    // pass 0: how many entries of this column are below its final threshold
+    int mine = 0;
+    for (int sh = 0; sh < nlists; ++sh) {
+        const u64* cl; const int n = list_of(sh, cl);
+        for (int e = 0; e < n; ++e) mine += ((uint32_t)(cl[(size_t)e * TILE] >> 32) < tau) ? 1 : 0;
+    }
+    // exclusive scan over the 128 threads
+    int incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+    if (lane == 31) s_wsum[warp] = incl;
+    __syncthreads();
+    int offset = incl - mine, total = 0;
+#pragma unroll
+    for (int w = 0; w < TILE / 32; ++w) { const int v = s_wsum[w]; if (w < warp) offset += v; total += v; }
+
+    u64 best[K];
+#pragma unroll
+    for (int r = 0; r < K; ++r) best[r] = ~0ull;
+    int nviol = 0;
+    for (int base = 0; base < total; base += VCAP) {
+        // this thread's items that fall into [base, base + VCAP)
+        if (offset < base + VCAP && offset + mine > base) {
+            int idx = offset;
+            for (int sh = 0; sh < nlists; ++sh) {
+                const u64* cl; const int n = list_of(sh, cl);
+                for (int e = 0; e < n; ++e) {
+                    const u64 ce = cl[(size_t)e * TILE];
+                    if ((uint32_t)(ce >> 32) >= tau) continue;
+                    if (idx >= base && idx < base + VCAP) {
+                        s_row[idx - base] = (uint32_t)(ce & 0xffffffffull);
+                        s_lb[idx - base] = dec_f((uint32_t)(ce >> 32));
+                        s_col[idx - base] = (uint16_t)tid;
+                    }
+                    ++idx;
+                }
+            }
+        }
+        __syncthreads();
+        const int cnt = min(VCAP, total - base);
+        for (int w = tid; w < cnt; w += TILE) {
+            const uint32_t i = s_row[w];
+            const int col = s_col[w];
+            const float* xp = prm.XR + ((int64_t)pd->xa_row0 + i) * k;      // 4k contiguous bytes
+            for (int c = 0; c < k; c += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(xp + c));
+            const float* yq = s_y + col;
             float acc = 0.f;
             if ((k & 3) == 0) {
-#pragma unroll 4
+#pragma unroll 8
                 for (int c = 0; c < k; c += 4) {
                     const float4 xv = __ldg(reinterpret_cast<const float4*>(xp + c));
-                    acc = fmaf(xv.x, __ldg(yp + (int64_t)c * prm.ld2_total), acc);
-                    acc = fmaf(xv.y, __ldg(yp + (int64_t)(c + 1) * prm.ld2_total), acc);
-                    acc = fmaf(xv.z, __ldg(yp + (int64_t)(c + 2) * prm.ld2_total), acc);
-                    acc = fmaf(xv.w, __ldg(yp + (int64_t)(c + 3) * prm.ld2_total), acc);
+                    acc = fmaf(xv.x, yq[c * TILE], acc);
+                    acc = fmaf(xv.y, yq[(c + 1) * TILE], acc);
+                    acc = fmaf(xv.z, yq[(c + 2) * TILE], acc);
+                    acc = fmaf(xv.w, yq[(c + 3) * TILE], acc);
                 }
             } else {
 #pragma unroll 8
-                for (int c = 0; c < k; ++c) acc = fmaf(__ldg(xp + c), __ldg(yp + (int64_t)c * prm.ld2_total), acc);
+                for (int c = 0; c < k; ++c) acc = fmaf(__ldg(xp + c), yq[c * TILE], acc);
             }
-            const float v = __fadd_rn(__fadd_rn(acc, __ldg(prm.nx + pd->x_col0 + i)), nyj);
-            ++nver;
-            if (dec_f((uint32_t)(ce >> 32)) > v) ++nviol;         // the lower bound must hold: assumption A's run-time check
+            const float v = __fadd_rn(__fadd_rn(acc, __ldg(prm.nx + pd->x_col0 + i)), s_ny[col]);
+            if (s_lb[w] > v) ++nviol;         // the lower bound must hold: assumption A's run-time check
             const u64 key = tc_make_key(__fsqrt_rn(fmaxf(v, 0.f)), i);
-            if (K == 1) best[0] = key < best[0] ? key : best[0];
-            else if (key < best[K - 1]) tc_insert5(reinterpret_cast<u64(&)[5]>(best), key);
+            if (K == 1) atomicMin(&s_best[col], key);
+            else s_key[w] = key;
+        }
+        __syncthreads();
+        if (K != 1) {
+            const int lo = max(offset, base), hi = min(offset + mine, base + VCAP);
+            for (int w = lo; w < hi; ++w) {
+                const u64 key = s_key[w - base];
+                if (key < best[K - 1]) tc_insert5(reinterpret_cast<u64(&)[5]>(best), key);
+            }
+            __syncthreads();
         }
     }
-    if (K == 1) {
-        atomicMin(prm.best + yc, best[0]);
-    } else {
-        const int64_t M = 5ll * n2;
-        int64_t* o = prm.out5 + (prm.cand_is_out_layout ? pd->out_off : 2ll * pd->cand0);
-        const int64_t r1 = (prm.flags & F2P_INT16_COMPAT) ? (int64_t)(int16_t)(uint16_t)(j & 0xffff) : (int64_t)j;
+    if (j < n2) {
+        if (K == 1) {
+            if (s_best[tid] != ~0ull) atomicMin(prm.best + yc, s_best[tid]);
+        } else {
+            const int64_t M = 5ll * n2;
+            int64_t* o = prm.out5 + (prm.cand_is_out_layout ? pd->out_off : 2ll * pd->cand0);
+            const int64_t r1 = (prm.flags & F2P_INT16_COMPAT) ? (int64_t)(int16_t)(uint16_t)(j & 0xffff) : (int64_t)j;
 #pragma unroll
-        for (int r = 0; r < K; ++r) {
-            o[5ll * j + r] = (int64_t)(uint32_t)(best[r] & 0xffffffffull);
-            if (!(prm.flags & F2P_ROW0_ONLY)) o[M + 5ll * j + r] = r1;
+            for (int r = 0; r < K; ++r) {
+                o[5ll * j + r] = (int64_t)(uint32_t)(best[r] & 0xffffffffull);
+                if (!(prm.flags & F2P_ROW0_ONLY)) o[M + 5ll * j + r] = r1;
+            }
         }
     }
     if (prm.stats) {
-        if (nver) atomicAdd(prm.stats + 2, nver);
-        if (nviol) atomicAdd(prm.stats + 3, nviol);
+        int nv = mine, vi = nviol;
+#pragma unroll
+        for (int m = 16; m >= 1; m >>= 1) { nv += __shfl_xor_sync(0xffffffffu, nv, m); vi += __shfl_xor_sync(0xffffffffu, vi, m); }
+        if (lane == 0) {
+            if (nv) atomicAdd(prm.stats + 2, (unsigned long long)nv);
+            if (vi) atomicAdd(prm.stats + 3, (unsigned long long)vi);
+        }
     }
 }
 
@@ -901,8 +975,14 @@ int launch_tc(int top5, const float* xT, int64_t ld1_total, const float* nx, con
     vp.XR = w.XR; vp.nx = nx; vp.yT = yT; vp.ld2_total = ld2_total; vp.ny = ny;
     vp.tau = w.tau; vp.cand = w.cand; vp.ccnt = w.ccnt; vp.tcflag = w.tcflag; vp.best = best; vp.out5 = out5;
     vp.cand_is_out_layout = cand_is_out_layout; vp.flags = flags; vp.stats = w.stats;
-    if (top5) nn_tc_verify_kernel<5><<<total_ytiles, TILE, 0, stream>>>(vp);
-    else nn_tc_verify_kernel<1><<<total_ytiles, TILE, 0, stream>>>(vp);
+    const size_t vsmem = (size_t)k * TILE * sizeof(float);
+    if (top5) {
+        F2P_CUDA(cudaFuncSetAttribute(nn_tc_verify_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vsmem));
+        nn_tc_verify_kernel<5><<<total_ytiles, TILE, vsmem, stream>>>(vp);
+    } else {
+        F2P_CUDA(cudaFuncSetAttribute(nn_tc_verify_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vsmem));
+        nn_tc_verify_kernel<1><<<total_ytiles, TILE, vsmem, stream>>>(vp);
+    }
     F2P_CUDA(cudaGetLastError());
     return 0;
 }
