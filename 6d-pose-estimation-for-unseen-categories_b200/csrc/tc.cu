@@ -225,6 +225,7 @@ nn_tc_screen_kernel(const __grid_constant__ CUtensorMap mapXA, const __grid_cons
     uint64_t* tempty = bars + 19;       // 2
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 21);
     int* s_flag = reinterpret_cast<int*>(s_tmem + 1);
+    uint32_t* s_T = reinterpret_cast<uint32_t*>(s_tmem + 2);       // [TILE] smallest threshold any epilogue thread of the column holds
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t rank = (CG == 2) ? cluster_ctarank() : 0u;
@@ -264,6 +265,7 @@ nn_tc_screen_kernel(const __grid_constant__ CUtensorMap mapXA, const __grid_cons
         fence_barrier_init();
     }
     if (warp == 1) { if (CG == 2) tmem_alloc512_2sm(s_tmem); else tmem_alloc512(s_tmem); }
+    if (tid >= 64 && tid < 64 + TILE) s_T[tid - 64] = ENC_INF;
     tc_fence_before();
     if (CG == 2) cluster_sync_all(); else __syncthreads();
     tc_fence_after();
@@ -368,6 +370,13 @@ nn_tc_screen_kernel(const __grid_constant__ CUtensorMap mapXA, const __grid_cons
         };
 
         const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * CHUNKS * 32);
+        // value e (0..7) of eight registers without a local-memory round trip: 7 selects
+        auto sel8 = [](const float* c, int e) -> float {
+            const bool b0 = e & 1, b1 = e & 2, b2 = e & 4;
+            const float a0 = b0 ? c[1] : c[0], a1 = b0 ? c[3] : c[2], a2 = b0 ? c[5] : c[4], a3 = b0 ? c[7] : c[6];
+            const float d0 = b1 ? a1 : a0, d1 = b1 ? a3 : a2;
+            return b2 ? d1 : d0;
+        };
         for (int t = 0; t < ntiles; ++t) {
             const int buf = t & 1;
             const int tile = t_begin + t;
@@ -380,6 +389,29 @@ nn_tc_screen_kernel(const __grid_constant__ CUtensorMap mapXA, const __grid_cons
             const uint32_t taddr = lane_addr + (uint32_t)(buf * TC_N);
             const uint32_t rowbase = (uint32_t)(tile * TC_N + half * CHUNKS * 32);
             float va[32], vb[32];
+            if (K > 1 && t == 0) {
+                // Cold start of a top-K scan: instead of tightening the threshold one record at a time (K ln(rows / K)
+                // records per thread in the first tile), take the K-th smallest of this thread's 4 * CHUNKS group minima:
+                // K different groups hold a value <= it, so it bounds the K-th smallest lower bound, and + W the K-th
+                // smallest UPPER bound — a valid threshold found without a single record.  The tile is then read again.
+                float gm[K];
+#pragma unroll
+                for (int r = 0; r < K; ++r) gm[r] = INF;
+                for (int c = 0; c < CHUNKS; ++c) {
+                    __syncwarp();
+                    tmem_ld32(taddr + (uint32_t)(c * 32), va);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const float m0 = min3f(va[8 * q], va[8 * q + 1], va[8 * q + 2]);
+                        const float m1 = min3f(va[8 * q + 3], va[8 * q + 4], va[8 * q + 5]);
+                        float u = min3f(m0, m1, fminf(va[8 * q + 6], va[8 * q + 7]));
+#pragma unroll
+                        for (int r = 0; r < K; ++r) { const float t2 = gm[r]; const bool p = u < t2; gm[r] = p ? u : t2; u = p ? t2 : u; }
+                    }
+                }
+                if (live && 4 * CHUNKS >= K) { Tg = fminf(Tg, __fadd_ru(gm[K - 1], Wt)); T = fminf(T, Tg); }
+            }
             __syncwarp();
             tmem_ld32(taddr, va);
 #pragma unroll
@@ -395,6 +427,9 @@ nn_tc_screen_kernel(const __grid_constant__ CUtensorMap mapXA, const __grid_cons
                     __syncwarp();
                     if (lane == 0) { if (CG == 2) mbar_arrive_remote(&tempty[buf], 0); else mbar_arrive(&tempty[buf]); }
                 }
+                // the other epilogue thread(s) of this column may have found a tighter threshold
+                if (EH > 1 && live) { Tg = fminf(Tg, dec_f(s_T[col])); T = fminf(T, Tg); }
+                const float T_c = T;
                 float g[4];
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
@@ -404,29 +439,25 @@ nn_tc_screen_kernel(const __grid_constant__ CUtensorMap mapXA, const __grid_cons
                 }
                 const float cm = fminf(fminf(g[0], g[1]), fminf(g[2], g[3]));
                 if (cm < T) {
-                    // rare: copy the groups that hold a passing value to local memory and walk their set bits — one
-                    // record() site instead of 32 predicated copies of it
-                    float tmp[32];
-                    uint32_t mask = 0;
+                    // rare: walk the passing values of every group that holds one (mask + register select: no local memory)
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         if (g[q] < T) {
+                            uint32_t m8 = 0;
 #pragma unroll
-                            for (int e = 0; e < 8; ++e) {
-                                tmp[8 * q + e] = cur[8 * q + e];
-                                mask |= (cur[8 * q + e] < T ? 1u : 0u) << (8 * q + e);
+                            for (int e = 0; e < 8; ++e) m8 |= (cur[8 * q + e] < T ? 1u : 0u) << e;
+                            while (m8) {
+                                const int e = __ffs(m8) - 1;
+                                m8 &= m8 - 1;
+                                const float v = sel8(&cur[8 * q], e);
+                                if (v < T) record(v, rowbase + (uint32_t)(c * 32 + 8 * q + e), Wt);
                             }
                         }
                     }
-                    while (mask) {
-                        const int e = __ffs(mask) - 1;
-                        mask &= mask - 1;
-                        const float v = tmp[e];
-                        if (v < T) record(v, rowbase + (uint32_t)(c * 32 + e), Wt);
-                    }
+                    if (EH > 1 && T < T_c && live) atomicMin(&s_T[col], enc_f(T));
                 }
             }
-            if (T < T_in && ub[K - 1] < Tg) { atomicMin(taup, enc_f(ub[K - 1])); }
+            if (T < T_in && live) { atomicMin(taup, enc_f(T)); }
         }
         // survivors of this CTA: entries still below its final threshold
         if (!dummy) {
@@ -859,7 +890,7 @@ int tc_kp(int k) { return (k + 6 + 7) / 8 * 8; }
 static size_t tc_smem_bytes(int kp, int eh, int cap, int* nstage_out) {
     const int nkb = (kp + TC_KB - 1) / TC_KB;
     const size_t stage = (size_t)(TC_B_STAGE / TC_CG) * sizeof(float);
-    const size_t fixed = (size_t)nkb * TC_A_BLOCK * sizeof(float) + (size_t)eh * cap * TILE * sizeof(u64) + 24 * sizeof(uint64_t);
+    const size_t fixed = (size_t)nkb * TC_A_BLOCK * sizeof(float) + (size_t)eh * cap * TILE * sizeof(u64) + 24 * sizeof(uint64_t) + TILE * sizeof(uint32_t);
     const size_t budget = 227 * 1024 - 1024;            // dynamic shared memory is 1024-aligned by the declaration
     int S = fixed >= budget ? 0 : (int)((budget - fixed) / stage);
     if (S > 8) S = 8;
