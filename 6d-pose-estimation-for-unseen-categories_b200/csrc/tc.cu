@@ -503,7 +503,8 @@ __device__ __forceinline__ void tc_insert5(u64 (&l)[5], u64 key) {
 struct TCVerifyParams {
     const PairDev* pairs; int npairs; int uniform_ytiles;
     int k, eh, cap;
-    const float* XR;        // [ld1_tc_total][k] exact FP32 rows of -2*feat_x (row-major copy made by the packing kernel)
+    const float* XR;        // [ld1_tc_total][kr] exact FP32 rows of -2*feat_x (row-major copy made by the packing kernel;
+                            // kr = round_up(k, 4), zero padded, so every row is read as float4)
     const float* nx;
     const float* yT; int64_t ld2_total; const float* ny;
     const uint32_t* tau; const u64* cand; const int* ccnt; const int* tcflag;
@@ -519,7 +520,7 @@ struct TCVerifyParams {
 // long-scoreboard stalls per issue).  So the tile's (column, row) items are flattened into one shared list and dealt out
 // to all 128 threads; the scene columns are staged in shared memory once, the CAD rows are L2-prefetched and read as
 // float4.  Arithmetic per item is unchanged (sequential-k fmaf, + nx, + ny, clamp, sqrt_rn).
-constexpr int VCAP = 1024;      // items per pass (a tile with more takes several passes)
+constexpr int VCAP = 2048;      // items per pass (a tile with more takes several passes)
 
 template <int K>
 __global__ void __launch_bounds__(TILE)
@@ -557,12 +558,25 @@ nn_tc_verify_kernel(const TCVerifyParams prm) {
         cl = prm.cand + slot * prm.cap * TILE + tid;
         return prm.ccnt[slot * TILE + tid];
     };
+    // Walks this column's lists, eight entries per step with all eight loads issued before any is used (a loop with one
+    // dependent L2 round trip per entry was most of this kernel's time on short scans: ncu, 8 % issue utilisation).
+    // Slots past the end read as ~0, whose encoded bound is above every threshold.
+    auto walk = [&](auto&& visit) {
+        for (int sh = 0; sh < nlists; ++sh) {
+            const u64* cl; const int n = list_of(sh, cl);
+            for (int e0 = 0; e0 < n; e0 += 8) {
+                u64 v[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) v[u] = (e0 + u < n) ? __ldg(cl + (size_t)(e0 + u) * TILE) : ~0ull;
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    if ((uint32_t)(v[u] >> 32) < tau) visit(v[u]);
+            }
+        }
+    };
     // pass 0: how many entries of this column are below its final threshold
     int mine = 0;
-    for (int sh = 0; sh < nlists; ++sh) {
-        const u64* cl; const int n = list_of(sh, cl);
-        for (int e = 0; e < n; ++e) mine += ((uint32_t)(cl[(size_t)e * TILE] >> 32) < tau) ? 1 : 0;
-    }
+    walk([&](u64) { ++mine; });
     // exclusive scan over the 128 threads
     int incl = mine;
 #pragma unroll
@@ -581,47 +595,70 @@ nn_tc_verify_kernel(const TCVerifyParams prm) {
         // this thread's items that fall into [base, base + VCAP)
         if (offset < base + VCAP && offset + mine > base) {
             int idx = offset;
-            for (int sh = 0; sh < nlists; ++sh) {
-                const u64* cl; const int n = list_of(sh, cl);
-                for (int e = 0; e < n; ++e) {
-                    const u64 ce = cl[(size_t)e * TILE];
-                    if ((uint32_t)(ce >> 32) >= tau) continue;
-                    if (idx >= base && idx < base + VCAP) {
-                        s_row[idx - base] = (uint32_t)(ce & 0xffffffffull);
-                        s_lb[idx - base] = dec_f((uint32_t)(ce >> 32));
-                        s_col[idx - base] = (uint16_t)tid;
-                    }
-                    ++idx;
+            walk([&](u64 ce) {
+                if (idx >= base && idx < base + VCAP) {
+                    s_row[idx - base] = (uint32_t)(ce & 0xffffffffull);
+                    s_lb[idx - base] = dec_f((uint32_t)(ce >> 32));
+                    s_col[idx - base] = (uint16_t)tid;
                 }
-            }
+                ++idx;
+            });
         }
         __syncthreads();
         const int cnt = min(VCAP, total - base);
-        for (int w = tid; w < cnt; w += TILE) {
-            const uint32_t i = s_row[w];
-            const int col = s_col[w];
-            const float* xp = prm.XR + ((int64_t)pd->xa_row0 + i) * k;      // 4k contiguous bytes
-            for (int c = 0; c < k; c += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(xp + c));
-            const float* yq = s_y + col;
-            float acc = 0.f;
-            if ((k & 3) == 0) {
-#pragma unroll 8
-                for (int c = 0; c < k; c += 4) {
-                    const float4 xv = __ldg(reinterpret_cast<const float4*>(xp + c));
-                    acc = fmaf(xv.x, yq[c * TILE], acc);
-                    acc = fmaf(xv.y, yq[(c + 1) * TILE], acc);
-                    acc = fmaf(xv.z, yq[(c + 2) * TILE], acc);
-                    acc = fmaf(xv.w, yq[(c + 3) * TILE], acc);
+        const int kr = (k + 3) & ~3, k4 = k & ~3;
+        // two items per thread and step: two independent k-long FMA chains in flight (each one is the reference's own
+        // sequential chain; nothing is reassociated)
+        for (int w = tid; w < cnt; w += 2 * TILE) {
+            const int w2 = w + TILE;
+            const bool two = w2 < cnt;
+            const uint32_t i0 = s_row[w], i1 = two ? s_row[w2] : i0;
+            const int col0 = s_col[w], col1 = two ? s_col[w2] : col0;
+            const float* xp0 = prm.XR + ((int64_t)pd->xa_row0 + i0) * kr;
+            const float* xp1 = prm.XR + ((int64_t)pd->xa_row0 + i1) * kr;
+            {   // rows of the NEXT step's two items towards L2 / L1 while this step computes
+                const int wn = w + 2 * TILE, wn2 = wn + TILE;
+                if (wn < cnt) {
+                    const float* q0 = prm.XR + ((int64_t)pd->xa_row0 + s_row[wn]) * kr;
+                    for (int c = 0; c < kr; c += 32) prefetch_l1(q0 + c);
+                    if (wn2 < cnt) {
+                        const float* q1 = prm.XR + ((int64_t)pd->xa_row0 + s_row[wn2]) * kr;
+                        for (int c = 0; c < kr; c += 32) prefetch_l1(q1 + c);
+                    }
                 }
-            } else {
-#pragma unroll 8
-                for (int c = 0; c < k; ++c) acc = fmaf(__ldg(xp + c), yq[c * TILE], acc);
             }
-            const float v = __fadd_rn(__fadd_rn(acc, __ldg(prm.nx + pd->x_col0 + i)), s_ny[col]);
-            if (s_lb[w] > v) ++nviol;         // the lower bound must hold: assumption A's run-time check
-            const u64 key = tc_make_key(__fsqrt_rn(fmaxf(v, 0.f)), i);
-            if (K == 1) atomicMin(&s_best[col], key);
-            else s_key[w] = key;
+            const float* yq0 = s_y + col0;
+            const float* yq1 = s_y + col1;
+            float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll 4
+            for (int c = 0; c < k4; c += 4) {
+                const float4 xv = __ldg(reinterpret_cast<const float4*>(xp0 + c));
+                const float4 xw = __ldg(reinterpret_cast<const float4*>(xp1 + c));
+                acc0 = fmaf(xv.x, yq0[c * TILE], acc0);             acc1 = fmaf(xw.x, yq1[c * TILE], acc1);
+                acc0 = fmaf(xv.y, yq0[(c + 1) * TILE], acc0);       acc1 = fmaf(xw.y, yq1[(c + 1) * TILE], acc1);
+                acc0 = fmaf(xv.z, yq0[(c + 2) * TILE], acc0);       acc1 = fmaf(xw.z, yq1[(c + 2) * TILE], acc1);
+                acc0 = fmaf(xv.w, yq0[(c + 3) * TILE], acc0);       acc1 = fmaf(xw.w, yq1[(c + 3) * TILE], acc1);
+            }
+            if (k4 < k) {
+                const float4 xv = __ldg(reinterpret_cast<const float4*>(xp0 + k4));
+                const float4 xw = __ldg(reinterpret_cast<const float4*>(xp1 + k4));
+                const float xa[3] = {xv.x, xv.y, xv.z}, xb[3] = {xw.x, xw.y, xw.z};
+#pragma unroll
+                for (int t = 0; t < 3; ++t)
+                    if (k4 + t < k) { acc0 = fmaf(xa[t], yq0[(k4 + t) * TILE], acc0); acc1 = fmaf(xb[t], yq1[(k4 + t) * TILE], acc1); }
+            }
+            const float v0 = __fadd_rn(__fadd_rn(acc0, __ldg(prm.nx + pd->x_col0 + i0)), s_ny[col0]);
+            const float v1 = __fadd_rn(__fadd_rn(acc1, __ldg(prm.nx + pd->x_col0 + i1)), s_ny[col1]);
+            if (s_lb[w] > v0) ++nviol;         // the lower bound must hold: assumption A's run-time check
+            const u64 key0 = tc_make_key(__fsqrt_rn(fmaxf(v0, 0.f)), i0);
+            if (K == 1) atomicMin(&s_best[col0], key0);
+            else s_key[w] = key0;
+            if (two) {
+                if (s_lb[w2] > v1) ++nviol;
+                const u64 key1 = tc_make_key(__fsqrt_rn(fmaxf(v1, 0.f)), i1);
+                if (K == 1) atomicMin(&s_best[col1], key1);
+                else s_key[w2] = key1;
+            }
         }
         __syncthreads();
         if (K != 1) {
@@ -742,7 +779,7 @@ tc_pack_kernel(const float* __restrict__ srcT, int64_t ld_total, const float* __
                 else v = 0.f;
                 if (!IS_X && !live) v = 0.f;
                 dst[(dst_row0 + r) * kp + c] = v;
-                if (IS_X && c < k) dst_exact[(dst_row0 + r) * k + c] = s[lane * PACK_LD + r];
+                if (IS_X && c < ((k + 3) & ~3)) dst_exact[(dst_row0 + r) * ((k + 3) & ~3) + c] = (c < k) ? s[lane * PACK_LD + r] : 0.f;
             }
         }
     }
@@ -912,7 +949,7 @@ size_t tc_ws_bytes(int64_t ld1_tc_total, int64_t ld2_total, int k, int64_t tc_it
     size_t b = 0;
     auto add = [&](size_t n) { b += (n + 255) & ~(size_t)255; };
     add(sizeof(float) * (size_t)ld1_tc_total * kp);                 // XA
-    add(sizeof(float) * (size_t)ld1_tc_total * k);                  // XR
+    add(sizeof(float) * (size_t)ld1_tc_total * ((k + 3) & ~3));     // XR
     add(sizeof(float) * (size_t)ld2_total * kp);                    // YA
     add(sizeof(uint32_t) * (size_t)ld2_total);                      // tau
     add(sizeof(u64) * (size_t)tc_items * TC_CG * TC_EH * cap * TILE);       // cand
@@ -928,7 +965,7 @@ void tc_ws_carve(TCWs& w, unsigned char* base, int64_t ld1_tc_total, int64_t ld2
     unsigned char* p = base;
     auto take = [&](size_t n) { unsigned char* q = p; p += (n + 255) & ~(size_t)255; return q; };
     w.XA = reinterpret_cast<float*>(take(sizeof(float) * (size_t)ld1_tc_total * kp));
-    w.XR = reinterpret_cast<float*>(take(sizeof(float) * (size_t)ld1_tc_total * k));
+    w.XR = reinterpret_cast<float*>(take(sizeof(float) * (size_t)ld1_tc_total * ((k + 3) & ~3)));
     w.YA = reinterpret_cast<float*>(take(sizeof(float) * (size_t)ld2_total * kp));
     w.tau = reinterpret_cast<uint32_t*>(take(sizeof(uint32_t) * (size_t)ld2_total));
     w.cand = reinterpret_cast<u64*>(take(sizeof(u64) * (size_t)tc_items * TC_CG * TC_EH * cap * TILE));
