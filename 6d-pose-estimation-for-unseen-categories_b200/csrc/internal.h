@@ -111,7 +111,7 @@ static inline int choose_tc_nsplit(long long base_items, int nrt, int sm) {   //
 }
 // Tensor-pipe path selection (F2P_NN_PATH=tc forces it, =gated / exact / two_phase disable it): by default problems with
 // at least TC_MIN_FLOPS of distance work whose k fills a 128-byte swizzle row.  Non-semantic: every path is exact.
-constexpr double TC_MIN_FLOPS = 4.0e10;
+constexpr double TC_MIN_FLOPS = 8.0e9;    // measured crossover (tools/sweep.py with F2P_NN_PATH forced both ways): batches win from 1.2e10, single pairs from 1.0e10, lose at 2.4e9
 bool tc_enabled(double flops, int k, int top5);
 bool tc_fits(int k, int top5);   // the resident scene tile + a >= 2-deep ring fit one SM's shared memory
 int measure_tf32_peak(double* tflops, cudaStream_t st);

@@ -436,7 +436,7 @@ def measure_workload(ctx, name, wl, ppg, steps, warmup, e2e_steps):
     # kernels of this library launched per step
     tiles = ppg * ((n1 + 127) // 128 + (n2 + 127) // 128)
     prep = 1 if tiles <= 8 * 148 else 2
-    tc = 2.0 * n1 * n2 * k * ppg >= 4.0e10 and k >= 19
+    tc = 2.0 * n1 * n2 * k * ppg >= 8.0e9 and k >= 19
     if spatial:
         k2 = (4 if tc else 0) + 3               # [pack x, pack y, screen, verify] + gated + exact fallback + merge
         launches = prep + k2 + 1 + 3 * 4        # + filter init + 3 x (vote, classify, verify, combine)
@@ -631,7 +631,7 @@ def roofline_section(ctx, wl, ppg=1, stages=None):
     pm, pb = _event_time(proj_x, 10, 3, flush)
     flops = 2.0 * n1 * n2 * k
     kp = (k + 6 + 7) // 8 * 8
-    tensor = flops >= 4.0e10 and k >= 19          # the library's own path selection (csrc/internal.h TC_MIN_FLOPS)
+    tensor = flops >= 8.0e9 and k >= 19          # the library's own path selection (csrc/internal.h TC_MIN_FLOPS)
     nm, nb = _event_time(nn, 10, 3, flush)        # default path
     stats = tc_stats(ctx) if tensor else None
     os.environ["F2P_NN_PATH"] = "gated"
