@@ -187,6 +187,42 @@ int f2p_nn_argmin_static(const float* xT, const float* nx, int n1, int ld1, cons
                          2.0 * n1 * (double)n2 * k, F2P_ROW0_ONLY, idx_out, aw, st, false, nullptr);
 }
 
+// ---- blocked arg-min (host pipelines that overlap the upload of a huge pair with its computation) ------------------
+int f2p_nn_argmin_keys(const float* xT, const float* nx, int n1, int ld1, int row0, const float* yT, const float* ny, int n2,
+                       int ld2, int k, unsigned long long* keys, void* ws_v, size_t ws_bytes, void* stream) {
+    if (!xT || !nx || !yT || !ny || !keys || !ws_v) { set_error("null pointer"); return F2P_EINVAL; }
+    if (k < 1 || n1 < 1 || n2 < 0 || row0 < 0) { set_error("bad shape n1=%d n2=%d k=%d row0=%d", n1, n2, k, row0); return F2P_EINVAL; }
+    if (k > F2P_MAX_K) { set_error("k=%d exceeds F2P_MAX_K", k); return F2P_ENOTSUP; }
+    if ((long long)row0 + n1 > 0x7ffffff0ll) { set_error("row0 + n1 exceeds the 31-bit row index"); return F2P_ENOTSUP; }
+    if (n2 == 0) return 0;
+    if (ws_bytes < f2p_nn_workspace_bytes(n1, n2, k, 0)) { set_error("workspace too small"); return F2P_ENOSPACE; }
+    PairDev p;
+    const int nrt = (n1 + TILE - 1) / TILE, nct = (n2 + TILE - 1) / TILE;
+    int rc = single_pair(p, n1, n2, ld1, ld2, pick_nsplit(nrt, nct));
+    if (rc) return rc;
+    if (ld2 != nct * TILE) { set_error("f2p_nn_argmin_keys needs ld2 == round_up(n2, %d)", TILE); return F2P_EINVAL; }
+    unsigned char* ws = static_cast<unsigned char*>(ws_v);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int items = p.nct * p.nsplit;
+    TCPlan tc;
+    const bool use_tc = single_pair_tc(p, k, 0, tc);
+    if (use_tc) {
+        size_t off = (256 + argmin_ws_bytes(ld2, k, 1) + 255) & ~(size_t)255;
+        tc_ws_carve(tc.ws, ws + off, tc.ld1_tc_total, ld2, k, tc.total_items, p.nct, 1, 0);
+    }
+    F2P_CUDA(cudaMemcpyAsync(ws, &p, sizeof(p), cudaMemcpyHostToDevice, st));
+    ArgminWs aw;
+    argmin_ws_carve(aw, ws + 256, ld2, k, 1);
+    return launch_argmin_keys(xT, ld1, nx, yT, ld2, ny, k, reinterpret_cast<const PairDev*>(ws), items, p.nct, n2,
+                              (uint32_t)row0, keys, aw, st, use_tc ? &tc : nullptr);
+}
+
+int f2p_keys_to_map(const unsigned long long* keys, int n2, unsigned flags, int64_t* out, void* stream) {
+    if (!keys || !out) { set_error("null pointer"); return F2P_EINVAL; }
+    if (n2 < 0) { set_error("bad n2=%d", n2); return F2P_EINVAL; }
+    return launch_keys_to_map(keys, n2, flags, out, static_cast<cudaStream_t>(stream));
+}
+
 size_t f2p_filter_workspace_bytes(int M) { return 256 + filter_pair_bytes(M < 0 ? 0 : M); }
 
 int f2p_spatial_filter(const float* cad, int ncad, const float* pc, int npc, const int64_t* p, int M,

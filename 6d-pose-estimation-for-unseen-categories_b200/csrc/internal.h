@@ -64,6 +64,10 @@ int launch_argmin(const float* xT, int64_t ld1_total, const float* nx, const flo
                   const float* ny, int k, const PairDev* pairs_dev, int npairs, int uniform_items, int total_items,
                   int uniform_ytiles, int total_ytiles, double flops, unsigned flags, int64_t* out, const ArgminWs& w,
                   cudaStream_t stream, bool pre_init = false, const TCPlan* tc = nullptr);
+int launch_argmin_keys(const float* xT, int64_t ld1, const float* nx, const float* yT, int64_t ld2, const float* ny, int k,
+                       const PairDev* pair_dev, int items, int ytiles, int n2, uint32_t row0, unsigned long long* keys,
+                       const ArgminWs& w, cudaStream_t stream, const TCPlan* tc);
+int launch_keys_to_map(const unsigned long long* keys, int n2, unsigned flags, int64_t* out, cudaStream_t stream);
 int launch_top5(const float* xT, int64_t ld1_total, const float* nx, const float* yT, int64_t ld2_total, const float* ny,
                 int k, const PairDev* pairs_dev, int npairs, int uniform_items, int total_items, int uniform_ytiles,
                 int total_ytiles, unsigned flags, unsigned long long* part5, int64_t* cand, int cand_is_out_layout,

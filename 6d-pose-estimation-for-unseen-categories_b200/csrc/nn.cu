@@ -1068,6 +1068,55 @@ int launch_argmin(const float* xT, int64_t ld1_total, const float* nx, const flo
     return 0;
 }
 
+// ---- blocked arg-min: one (row block, column block) of a pair, merged into persistent keys -----------------------
+// keys[j] = min over every block processed so far of (bits(d) << 32 | global row): order = (distance, row), so exact
+// ties still go to the lowest CAD row of the whole pair, whatever order the row blocks arrive in.
+__global__ void __launch_bounds__(256)
+merge_keys_kernel(const u64* __restrict__ best, int n2, uint32_t row0, u64* __restrict__ keys) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n2) return;
+    const u64 kx = best[j];
+    if ((uint32_t)(kx & 0xffffffffull) >= IDX_NONE) return;       // no finite distance in this block
+    atomicMin(keys + j, kx + (u64)row0);
+}
+__global__ void __launch_bounds__(256)
+keys_to_map_kernel(const u64* __restrict__ keys, int n2, unsigned flags, int64_t* __restrict__ out) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n2) return;
+    uint32_t idx = (uint32_t)(keys[j] & 0xffffffffull);
+    if (idx >= IDX_NONE) idx = 0;      // all distances +inf/NaN: out of contract, mirror argmin's first index
+    out[j] = (int64_t)idx;
+    out[(int64_t)n2 + j] = row1_value(j, flags);
+}
+
+int launch_argmin_keys(const float* xT, int64_t ld1, const float* nx, const float* yT, int64_t ld2, const float* ny, int k,
+                       const PairDev* pair_dev, int items, int ytiles, int n2, uint32_t row0, u64* keys, const ArgminWs& w,
+                       cudaStream_t stream, const TCPlan* tc) {
+    if (items <= 0 || ytiles <= 0) return 0;
+    NNParams prm;
+    prm.pairs = pair_dev; prm.npairs = 1; prm.uniform_items = items; prm.k = k;
+    prm.nx = nx; prm.ny = ny; prm.best = w.best; prm.part5 = nullptr; prm.best2 = nullptr; prm.ncols = nullptr;
+    prm.tileflag = nullptr; prm.tilecnt = nullptr; prm.out = nullptr; prm.flags = F2P_ROW0_ONLY;
+    int rc;
+    argmin_init_kernel<<<(unsigned)((ld2 + 255) / 256), 256, 0, stream>>>(w.best, nullptr, nullptr, (size_t)ld2, nullptr, 0, nullptr);
+    if (tc) {
+        if ((rc = launch_tc(0, xT, ld1, nx, yT, ld2, ny, k, pair_dev, 1, tc->uni_items, tc->total_items, tc->uni_xtiles,
+                            tc->total_xtiles, ytiles, ytiles, tc->ld1_tc_total, F2P_ROW0_ONLY, w.best, nullptr, 0, tc->ws, stream))) return rc;
+        prm.ncols = tc->ws.tcflag;
+    }
+    if ((rc = launch_gated<1>(xT, ld1, yT, ld2, k, prm, items, stream))) return rc;
+    merge_keys_kernel<<<(unsigned)((n2 + 255) / 256), 256, 0, stream>>>(w.best, n2, row0, keys);
+    F2P_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int launch_keys_to_map(const u64* keys, int n2, unsigned flags, int64_t* out, cudaStream_t stream) {
+    if (n2 <= 0) return 0;
+    keys_to_map_kernel<<<(unsigned)((n2 + 255) / 256), 256, 0, stream>>>(keys, n2, flags, out);
+    F2P_CUDA(cudaGetLastError());
+    return 0;
+}
+
 int launch_top5(const float* xT, int64_t ld1_total, const float* nx, const float* yT, int64_t ld2_total, const float* ny,
                 int k, const PairDev* pairs_dev, int npairs, int uniform_items, int total_items, int uniform_ytiles,
                 int total_ytiles, unsigned flags, u64* part5, int64_t* cand, int cand_is_out_layout, cudaStream_t stream,

@@ -56,6 +56,9 @@ _SIGNATURES = {
                                      ctypes.c_int, _c_vp, _c_vp, ctypes.c_size_t, _c_vp]),
     "f2p_nn_argmin_static": (ctypes.c_int, [_c_vp, _c_vp, ctypes.c_int, ctypes.c_int, _c_vp, _c_vp, ctypes.c_int, ctypes.c_int,
                                             ctypes.c_int, _c_vp, _c_vp]),
+    "f2p_nn_argmin_keys": (ctypes.c_int, [_c_vp, _c_vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, _c_vp, _c_vp, ctypes.c_int,
+                                          ctypes.c_int, ctypes.c_int, _c_vp, _c_vp, ctypes.c_size_t, _c_vp]),
+    "f2p_keys_to_map": (ctypes.c_int, [_c_vp, ctypes.c_int, ctypes.c_uint, _c_vp, _c_vp]),
     "f2p_nn_top5": (ctypes.c_int, [_c_vp, _c_vp, ctypes.c_int, ctypes.c_int, _c_vp, _c_vp, ctypes.c_int, ctypes.c_int,
                                    ctypes.c_int, _c_vp, _c_vp, ctypes.c_size_t, _c_vp]),
     "f2p_spatial_filter": (ctypes.c_int, [_c_vp, ctypes.c_int, _c_vp, ctypes.c_int, _c_vp, ctypes.c_int,

@@ -205,3 +205,108 @@ def naive_host_pipelined(C12, evecs_x, evecs_y, chunks=4, int16_compat=False):
         d2h.synchronize()
     return out_h
 
+
+
+def naive_host_blocked(C12, evecs_x, evecs_y, xb=2, yb=2, int16_compat=False):
+    """`naive_fmap2pointmap` for ONE large host-resident pair with the upload hidden behind the kernels.
+
+    A single pair has no pair groups to pipeline, and its kernels (3.4 ms at 100k x 100k x 128) now take little longer than
+    its upload (102 MB, ~2 ms), so the pair is cut into xb row blocks of the CAD basis and yb column blocks of the scene
+    basis: block (i, j) is an independent arg-min whose exact (distance, global row) keys are merged into the scene
+    block's persistent keys (`f2p_nn_argmin_keys`), so the result is bit-identical to the one-shot call.  Pieces are
+    uploaded in the order the blocks need them (x0, y0, x1, ..., y1, ...) on the copy stream; only the first two are
+    exposed.  Every piece is projected / transposed once (`f2p_project`).  Returns int64 [2, V2] as a pinned host tensor."""
+    import ctypes
+    lib = _lib.load()
+    C = C12.squeeze(0) if C12.dim() == 3 else C12
+    ex = evecs_x.squeeze(0) if evecs_x.dim() == 3 else evecs_x
+    ey = evecs_y.squeeze(0) if evecs_y.dim() == 3 else evecs_y
+    for t in (C, ex, ey):
+        if not isinstance(t, torch.Tensor) or t.is_cuda or t.dim() != 2:
+            raise ValueError("naive_host_blocked takes 2-D HOST tensors (one pair)")
+    n1, k = (int(v) for v in ex.shape)
+    n2 = int(ey.shape[0])
+    if C.shape[0] != k or C.shape[1] != k or ey.shape[1] != k:
+        raise RuntimeError(f"shapes {tuple(ex.shape)} @ {tuple(C.shape)}^T vs {tuple(ey.shape)} are inconsistent")
+    if n1 < 1:
+        raise RuntimeError("evecs_x has no rows (argmin of an empty dimension)")
+    out_h = _pinned("nvb", (2, n2), torch.int64)
+    if n2 == 0:
+        return out_h
+    device = _device()
+    C, ex, ey = C.float().contiguous(), ex.float().contiguous(), ey.float().contiguous()
+
+    def cuts(n, parts):      # block boundaries, multiples of 128
+        step = ((n + parts - 1) // parts + 127) // 128 * 128
+        return [(lo, min(n, lo + step)) for lo in range(0, n, step)]
+    xcut, ycut = cuts(n1, max(1, int(xb))), cuts(n2, max(1, int(yb)))
+    with torch.cuda.device(device):
+        comp = torch.cuda.current_stream(device)
+        h2d, d2h = _copy_streams(device)
+        h2d.wait_stream(comp)
+        st = _lib.stream_ptr(device)
+        ld1 = [((hi - lo) + 127) // 128 * 128 for lo, hi in xcut]
+        ld2 = [((hi - lo) + 127) // 128 * 128 for lo, hi in ycut]
+        C_d = torch.empty((k, k), dtype=torch.float32, device=device)
+        ex_d = torch.empty((n1, k), dtype=torch.float32, device=device)
+        ey_d = torch.empty((n2, k), dtype=torch.float32, device=device)
+        xT = [torch.empty((k, l), dtype=torch.float32, device=device) for l in ld1]
+        nx = [torch.empty((l,), dtype=torch.float32, device=device) for l in ld1]
+        yT = [torch.empty((k, l), dtype=torch.float32, device=device) for l in ld2]
+        ny = [torch.empty((l,), dtype=torch.float32, device=device) for l in ld2]
+        keys = [torch.full((l,), -1, dtype=torch.int64, device=device) for l in ld2]          # every byte 0xFF
+        out_d = torch.empty((2, n2), dtype=torch.int64, device=device)
+        wsp = _lib.workspace(device, lib.f2p_project_workspace_bytes() +
+                             max(lib.f2p_nn_workspace_bytes(b - a, d - c, k, 0) for a, b in xcut for c, d in ycut) + 1024)
+        pbytes = (lib.f2p_project_workspace_bytes() + 255) // 256 * 256
+        ws_nn = wsp[pbytes:]
+        for t in (C_d, ex_d, ey_d):
+            t.record_stream(h2d)
+        # uploads, in the order the blocks need them
+        ev_x, ev_y = [None] * len(xcut), [None] * len(ycut)
+
+        def up(dst, src, lo, hi):
+            with torch.cuda.stream(h2d):
+                dst[lo:hi].copy_(src[lo:hi], non_blocking=True)
+                e = torch.cuda.Event(); e.record(h2d)
+            return e
+        with torch.cuda.stream(h2d):
+            C_d.copy_(C, non_blocking=True)
+        order = [("x", 0), ("y", 0)] + [("x", i) for i in range(1, len(xcut))] + [("y", j) for j in range(1, len(ycut))]
+        for kind, i in order:
+            if kind == "x":
+                ev_x[i] = up(ex_d, ex, *xcut[i])
+            else:
+                ev_y[i] = up(ey_d, ey, *ycut[i])
+        done_x, done_y = [False] * len(xcut), [False] * len(ycut)
+        for j, (c0, c1) in enumerate(ycut):
+            if not done_y[j]:
+                comp.wait_event(ev_y[j])
+                _lib.check(lib.f2p_project(ey_d[c0:c1].data_ptr(), c1 - c0, k, k, None, yT[j].data_ptr(), ny[j].data_ptr(), ld2[j],
+                                           wsp.data_ptr(), pbytes, st), "f2p_project")
+                done_y[j] = True
+            for i, (r0, r1) in enumerate(xcut):
+                if not done_x[i]:
+                    comp.wait_event(ev_x[i])
+                    _lib.check(lib.f2p_project(ex_d[r0:r1].data_ptr(), r1 - r0, k, k, C_d.data_ptr(), xT[i].data_ptr(),
+                                               nx[i].data_ptr(), ld1[i], wsp.data_ptr(), pbytes, st), "f2p_project")
+                    done_x[i] = True
+                _lib.check(lib.f2p_nn_argmin_keys(xT[i].data_ptr(), nx[i].data_ptr(), r1 - r0, ld1[i], r0, yT[j].data_ptr(),
+                                                  ny[j].data_ptr(), c1 - c0, ld2[j], k, keys[j].data_ptr(), ws_nn.data_ptr(),
+                                                  ws_nn.numel(), st), "f2p_nn_argmin_keys")
+        # keys -> map, block by block (row 1 is the scene point index of the whole pair)
+        flags = _lib.F2P_INT16_COMPAT if int16_compat else 0
+        tmp = torch.empty((2, max(ld2)), dtype=torch.int64, device=device)
+        for j, (c0, c1) in enumerate(ycut):
+            w = c1 - c0
+            _lib.check(lib.f2p_keys_to_map(keys[j].data_ptr(), w, 0, tmp.data_ptr(), st), "f2p_keys_to_map")
+            out_d[0, c0:c1].copy_(tmp.view(-1)[:w])
+        idx = torch.arange(n2, dtype=torch.int64, device=device)
+        out_d[1].copy_(((idx + 32768) % 65536) - 32768 if int16_compat else idx)      # naive.py:21's int16 wrap, exactly
+        ev = torch.cuda.Event(); ev.record(comp)
+        out_d.record_stream(d2h)
+        with torch.cuda.stream(d2h):
+            d2h.wait_event(ev)
+            out_h.copy_(out_d, non_blocking=True)
+        d2h.synchronize()
+    return out_h

@@ -289,7 +289,7 @@ def pin_rank_to_its_numa_node(local_rank, world):
 def measure_workload(ctx, name, wl, ppg, steps, warmup, e2e_steps):
     """Resident and end-to-end throughput of one workload on this process group."""
     from fmap2pointmap_solvers.batched import naive_batched, spatial_batched
-    from fmap2pointmap_solvers.pipeline import naive_host_pipelined, spatial_host_pipelined
+    from fmap2pointmap_solvers.pipeline import naive_host_blocked, naive_host_pipelined, spatial_host_pipelined
     dev, dist, world, rank = ctx.dev, ctx.dist, ctx.world, ctx.rank
     n1, n2, k = wl["n1"], wl["n2"], wl["k"]
     spatial = wl["solver"] == "spatial"
@@ -360,6 +360,11 @@ def measure_workload(ctx, name, wl, ppg, steps, warmup, e2e_steps):
                 d2h_bytes[0] = int(2 * counts.max()) * 8 * flat.shape[0] + counts.numel() * 8   # upper bound: prefix width of the widest group
                 return flat
             res = naive_host_pipelined(host["C"], host["ex"], host["ey"])
+            d2h_bytes[0] = res.numel() * 8
+            return res
+        if not spatial and float(n1) * n2 >= 2e9:
+            # one huge pair: row / column blocks, uploads behind the kernels (pipeline.naive_host_blocked)
+            res = naive_host_blocked(host["C"][0], host["ex"][0], host["ey"][0])
             d2h_bytes[0] = res.numel() * 8
             return res
         src = {kk: v.to(dev, non_blocking=True) for kk, v in host.items()}

@@ -103,6 +103,18 @@ int f2p_nn_top5(const float* xT_dev, const float* nx_dev, int n1, int ld1,
                 const float* yT_dev, const float* ny_dev, int n2, int ld2, int k,
                 int64_t* idx5_out_dev, void* ws_dev, size_t ws_bytes, void* stream);
 
+/* Kernel 2 on ONE (row block, column block) of a pair, for host pipelines that overlap the upload of a huge pair with its
+ * computation (naive.py:33-34 evaluated block by block; fmap2pointmap_solvers/pipeline.py: naive_host_blocked).
+ * keys_dev[j] (u64, j < n2; set every byte to 0xFF before the first block) = min over the blocks processed so far of
+ * (bits(d_ij) << 32 | row0 + i): merging by (distance, global row) keeps the reference's lowest-index rule for exact ties
+ * across blocks, in whatever order they arrive.  xT / nx describe the block's n1 rows (global rows row0 .. row0 + n1 - 1),
+ * yT / ny its n2 scene points; workspace as for f2p_nn_argmin (f2p_nn_workspace_bytes(n1, n2, k, 0)). */
+int f2p_nn_argmin_keys(const float* xT_dev, const float* nx_dev, int n1, int ld1, int row0,
+                       const float* yT_dev, const float* ny_dev, int n2, int ld2, int k,
+                       unsigned long long* keys_dev, void* ws_dev, size_t ws_bytes, void* stream);
+/* keys -> the naive solver's int64 [2,n2] map (naive.py:21): row 0 = CAD row, row 1 = scene point index. */
+int f2p_keys_to_map(const unsigned long long* keys_dev, int n2, unsigned flags, int64_t* out_dev, void* stream);
+
 /* Kernel 3: spatial-consistency filter (spacial_filtering.py:51-75) on candidate pairs p[2][M] (row stride M).
  * Writes the survivors dense as int64 [2,M'] (row stride M') into out (2*M slots), *count_dev = M',
  * *status_dev bit0 = "skipped";

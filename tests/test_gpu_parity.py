@@ -1044,3 +1044,23 @@ def test_shared_cad_side_operands_match_per_pair_operands(solvers, oracle):
     for i in range(P):
         m = int(counts[i])
         assert torch.equal(flat[i, :2 * m].view(2, m), want_s[i].cpu())
+
+
+@pytest.mark.parametrize("path", ["gated", "tc"])
+def test_blocked_host_pipeline_matches_the_one_shot_call(solvers, oracle, path, monkeypatch):
+    """One pair cut into row x column blocks with persistent (distance, global row) keys: same map as the one-shot
+    solver, including exact ties between rows that land in DIFFERENT row blocks (lowest global row wins) and ragged blocks."""
+    from fmap2pointmap_solvers.pipeline import naive_host_blocked
+    from fmap2pointmap_solvers.synth import make_pair
+    monkeypatch.setenv("F2P_NN_PATH", path)
+    P = make_pair(3000, 1400, 64, seed=91)
+    ex = P.evecs_x.clone()
+    ex[2500:2600] = ex[100:200]          # exact duplicates across row blocks (block size 1024 / 1536)
+    ex[1700] = ex[5]
+    want = solvers.naive_fmap2pointmap(P.C12.cuda(), ex.cuda(), P.evecs_y.cuda()).cpu()
+    np.testing.assert_array_equal(want.numpy(), oracle.naive(P.C12, ex, P.evecs_y, int16_compat=False))
+    for xb, yb in ((2, 2), (3, 1), (1, 3), (4, 5)):
+        got = naive_host_blocked(P.C12, ex.pin_memory(), P.evecs_y, xb=xb, yb=yb)
+        assert not got.is_cuda and torch.equal(got, want), (xb, yb)
+    got16 = naive_host_blocked(P.C12.unsqueeze(0), ex, P.evecs_y, int16_compat=True)
+    assert torch.equal(got16, solvers.naive_fmap2pointmap(P.C12.cuda(), ex.cuda(), P.evecs_y.cuda(), int16_compat=True).cpu())
