@@ -71,6 +71,14 @@ _SIGNATURES = {
     "f2p_spatial_host": (ctypes.c_int, [_c_vp, _c_vp, ctypes.c_int, _c_vp, ctypes.c_int, ctypes.c_int, _c_vp, ctypes.c_int,
                                         _c_vp, ctypes.c_int, ctypes.POINTER(ctypes.c_float), ctypes.c_uint, _c_vp,
                                         ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]),
+    "f2p_pair_stream_create": (ctypes.c_int, [ctypes.c_int, ctypes.POINTER(_c_vp)]),
+    "f2p_pair_stream_destroy": (ctypes.c_int, [_c_vp]),
+    "f2p_pair_stream_submit_naive": (ctypes.c_int, [_c_vp, _c_vp, _c_vp, ctypes.c_int, _c_vp, ctypes.c_int, ctypes.c_int,
+                                                    ctypes.c_uint, _c_vp, ctypes.POINTER(ctypes.c_longlong)]),
+    "f2p_pair_stream_submit_spatial": (ctypes.c_int, [_c_vp, _c_vp, _c_vp, ctypes.c_int, _c_vp, ctypes.c_int, ctypes.c_int,
+                                                      _c_vp, ctypes.c_int, _c_vp, ctypes.c_int, ctypes.POINTER(ctypes.c_float),
+                                                      ctypes.c_uint, _c_vp, _c_vp, _c_vp, ctypes.POINTER(ctypes.c_longlong)]),
+    "f2p_pair_stream_flush": (ctypes.c_int, [_c_vp, ctypes.POINTER(ctypes.c_longlong)]),
     "f2p_inlier_ratio_batched": (ctypes.c_int, [_c_vp, _c_vp, _c_vp, ctypes.POINTER(F2PPairDesc), ctypes.c_int, ctypes.c_int,
                                                 _c_vp, ctypes.POINTER(ctypes.c_float), _c_vp, _c_vp, _c_vp,
                                                 ctypes.c_size_t, _c_vp]),

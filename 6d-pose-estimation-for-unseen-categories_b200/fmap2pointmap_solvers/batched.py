@@ -225,10 +225,40 @@ def _single_operands(C12, evecs_x, evecs_y, device):
     return C, ex, ey, k
 
 
+def _naive_single_host(lib, device, C12, evecs_x, evecs_y, int16_compat):
+    """All three operands in host memory: one `f2p_naive_host` call (include/f2p.h) — the library uploads from the
+    tensors' own memory into its per-thread staging, runs the kernels and writes the map into a host tensor; no torch
+    device tensors, allocations or stream work on the way."""
+    def host(t):
+        t = t.detach()
+        if t.dtype != torch.float32:
+            t = t.float()
+        return t if t.is_contiguous() else t.contiguous()
+    C, ex, ey = host(_squeeze_c(C12)), host(evecs_x), host(evecs_y)
+    if ex.dim() != 2 or ey.dim() != 2:
+        raise ValueError(f"expected 2-D tensors, got shapes {tuple(ex.shape)} and {tuple(ey.shape)}")
+    k = int(C.shape[0])
+    if ex.shape[1] != k or ey.shape[1] != k:
+        raise RuntimeError(f"pair 0: shapes {tuple(ex.shape)} @ {tuple(C.shape)}^T vs {tuple(ey.shape)} "
+                           f"are inconsistent (all pairs of a batch must share K={k})")
+    n1, n2 = int(ex.shape[0]), int(ey.shape[0])
+    if n1 < 1:
+        raise RuntimeError("pair 0: evecs_x has no rows (argmin of an empty dimension)")
+    out = torch.empty((2, n2), dtype=torch.int64)
+    if n2 > 0:
+        with torch.cuda.device(device):
+            rc = lib.f2p_naive_host(C.data_ptr(), ex.data_ptr(), n1, ey.data_ptr(), n2, k,
+                                    _lib.F2P_INT16_COMPAT if int16_compat else 0, out.data_ptr())
+        _lib.check(rc, "f2p_naive_host")
+    return out
+
+
 def naive_single(C12, evecs_x, evecs_y, int16_compat=False):
     """`naive_fmap2pointmap` for ONE pair: int64 [2,V2] on the device of `evecs_x`."""
     lib = _lib.load()
     device = _lib.cuda_device_for(evecs_x, evecs_y, C12)
+    if not (evecs_x.is_cuda or evecs_y.is_cuda or C12.is_cuda):
+        return _naive_single_host(lib, device, C12, evecs_x, evecs_y, int16_compat)
     with torch.cuda.device(device):
         C, ex, ey, k = _single_operands(C12, evecs_x, evecs_y, device)
         n1, n2 = int(ex.shape[0]), int(ey.shape[0])

@@ -310,3 +310,150 @@ def naive_host_blocked(C12, evecs_x, evecs_y, xb=2, yb=2, int16_compat=False):
             out_h.copy_(out_d, non_blocking=True)
         d2h.synchronize()
     return out_h
+
+
+def _host_f32(t, what):
+    if not isinstance(t, torch.Tensor) or t.is_cuda:
+        raise ValueError(f"{what}: the pair streams take HOST tensors")
+    t = t.detach()
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t if t.is_contiguous() else t.contiguous()
+
+
+class _NativePairStream:
+    """ctypes face of F2PPairStream (include/f2p.h): submissions complete in order; `pending` holds, per submission in
+    flight, the tensors the C side still reads from or writes to."""
+
+    def __init__(self, depth):
+        import collections
+        import ctypes
+        self.ct = ctypes
+        self.lib = _lib.load()
+        self.h = ctypes.c_void_p()
+        _lib.check(self.lib.f2p_pair_stream_create(int(depth), ctypes.byref(self.h)), "f2p_pair_stream_create")
+        self.pending = collections.deque()
+        self.completed = 0
+        self.popped = 0
+        self.done = ctypes.c_longlong(0)
+
+    def ready(self):
+        """Submissions whose results have arrived since the last call, oldest first."""
+        out = []
+        while self.popped < self.done.value:
+            out.append(self.pending.popleft())
+            self.popped += 1
+        return out
+
+    def flush(self):
+        _lib.check(self.lib.f2p_pair_stream_flush(self.h, self.ct.byref(self.done)), "f2p_pair_stream_flush")
+        return self.ready()
+
+    def close(self):
+        if self.h:
+            self.lib.f2p_pair_stream_destroy(self.h)
+            self.h = self.ct.c_void_p()
+
+    # Creating the object costs streams, events and (on first use) pinned and device allocations — far more than a
+    # pair — so finished generators hand their object back and the next stream on this thread / device / depth reuses it.
+    _idle = {}
+
+    @classmethod
+    def take(cls, device, depth):
+        import threading
+        key = (device.index, int(depth), threading.get_ident())
+        ps = cls._idle.pop(key, None)
+        if ps is None:
+            ps = cls(depth)
+        ps.key = key
+        return ps
+
+    def give_back(self, clean):
+        """Back to the idle pool after a complete run; an abandoned or failed run is flushed and destroyed."""
+        if clean and not self.pending and self.key not in self._idle:
+            self._idle[self.key] = self
+        else:
+            self.close()
+            self.pending.clear()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def naive_pair_stream(pairs, depth=3, int16_compat=False):
+    """`naive_fmap2pointmap` over a stream of host-resident pairs — the per-sample loop of `scripts/eval.py:83-91` with
+    `depth` pairs in flight (F2PPairStream, include/f2p.h): pair i+1 is uploaded and pair i-1 downloaded while pair i
+    runs.  `pairs` is any iterable of (C12, evecs_x, evecs_y) host tensors ([K,K] or [1,K,K]; shapes may differ from
+    pair to pair); results come back in order, one int64 [2,V2] host tensor per pair, each bit-identical to the single
+    call.  Pinned inputs keep the uploads asynchronous.
+
+        for p_pred in naive_pair_stream((s["C12"], s["evecs_x"], s["evecs_y"]) for s in samples): ...
+    """
+    from .batched import _squeeze_c
+    device = _device()
+    flags = _lib.F2P_INT16_COMPAT if int16_compat else 0
+    with torch.cuda.device(device):
+        ps, clean = _NativePairStream.take(device, depth), False
+        try:
+            for C12, ex, ey in pairs:
+                C, ex, ey = _host_f32(_squeeze_c(C12), "C12"), _host_f32(ex, "evecs_x"), _host_f32(ey, "evecs_y")
+                if ex.dim() != 2 or ey.dim() != 2 or ex.shape[1] != C.shape[0] or ey.shape[1] != C.shape[0]:
+                    raise RuntimeError(f"shapes {tuple(ex.shape)} @ {tuple(C.shape)}^T vs {tuple(ey.shape)} are inconsistent")
+                if ex.shape[0] < 1:
+                    raise RuntimeError("evecs_x has no rows (argmin of an empty dimension)")
+                out = torch.empty((2, ey.shape[0]), dtype=torch.int64)
+                _lib.check(ps.lib.f2p_pair_stream_submit_naive(ps.h, C.data_ptr(), ex.data_ptr(), ex.shape[0], ey.data_ptr(),
+                                                               ey.shape[0], C.shape[0], flags, out.data_ptr(),
+                                                               ps.ct.byref(ps.done)), "f2p_pair_stream_submit_naive")
+                ps.pending.append((out, C, ex, ey))
+                for item in ps.ready():
+                    yield item[0]
+            for item in ps.flush():
+                yield item[0]
+            clean = True
+        finally:
+            ps.give_back(clean)
+
+
+def spatial_pair_stream(samples, depth=3, int16_compat=True):
+    """`spacial_filtering_fmap2pointmap` over a stream of host-resident samples (C12, evecs_x, evecs_y, CAD, PC,
+    diam_cad), `depth` in flight; yields, in order, the int64 [2,M'] host map of every sample ([2,0] when the filter
+    leaves nothing), bit-identical to the single call."""
+    import ctypes
+    from .batched import _squeeze_c, thresholds
+    device = _device()
+    flags = _lib.F2P_INT16_COMPAT if int16_compat else 0
+
+    def result(item):
+        out, meta = item[0], item[1]
+        m = int(meta[0])
+        return out[:2 * m].view(2, m).clone() if m else torch.empty((2, 0), dtype=torch.int64)
+
+    with torch.cuda.device(device):
+        ps, clean = _NativePairStream.take(device, depth), False
+        try:
+            for C12, ex, ey, cad, pc, diam in samples:
+                C, ex, ey = _host_f32(_squeeze_c(C12), "C12"), _host_f32(ex, "evecs_x"), _host_f32(ey, "evecs_y")
+                cad, pc = _host_f32(cad, "CAD"), _host_f32(pc, "PC")
+                if ex.dim() != 2 or ey.dim() != 2 or ex.shape[1] != C.shape[0] or ey.shape[1] != C.shape[0]:
+                    raise RuntimeError(f"shapes {tuple(ex.shape)} @ {tuple(C.shape)}^T vs {tuple(ey.shape)} are inconsistent")
+                if cad.dim() != 2 or cad.shape[1] != 3 or pc.dim() != 2 or pc.shape[1] != 3:
+                    raise RuntimeError("CAD / PC must be [N,3]")
+                thr = (ctypes.c_float * 4)(*thresholds(diam))
+                out = torch.empty(max(10 * ey.shape[0], 1), dtype=torch.int64)
+                meta = torch.zeros(2, dtype=torch.int32)
+                _lib.check(ps.lib.f2p_pair_stream_submit_spatial(
+                    ps.h, C.data_ptr(), ex.data_ptr(), ex.shape[0], ey.data_ptr(), ey.shape[0], C.shape[0], cad.data_ptr(),
+                    cad.shape[0], pc.data_ptr(), pc.shape[0], thr, flags, out.data_ptr(), meta.data_ptr(),
+                    meta.data_ptr() + 4, ps.ct.byref(ps.done)), "f2p_pair_stream_submit_spatial")
+                ps.pending.append((out, meta, C, ex, ey, cad, pc))
+                for item in ps.ready():
+                    yield result(item)
+            for item in ps.flush():
+                yield result(item)
+            clean = True
+        finally:
+            ps.give_back(clean)

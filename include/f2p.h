@@ -220,13 +220,35 @@ int f2p_compute_tims(const double* v_dev, int n, double* vtilde_dev, int32_t* ma
 
 /* ---- host-buffer convenience (what a non-torch caller binds; copies are inside the call) ------------- */
 
-/* Single pair, HOST pointers in and out; synchronous.  out_host: naive [2,n2]; spatial: 2*5*n2 slots, the first
- * 2*(*count) hold the dense [2,M'] result. */
+/* Single pair, HOST pointers in and out; synchronous (one submission + flush on a per-thread pair stream of depth 1,
+ * so repeated calls allocate nothing).  out_host: naive [2,n2]; spatial: room for 2*5*n2 slots, the first 2*(*count)
+ * receive the dense [2,M'] result. */
 int f2p_naive_host(const float* C_host, const float* evecs_x_host, int n1, const float* evecs_y_host, int n2,
                    int k, unsigned flags, int64_t* out_host);
 int f2p_spatial_host(const float* C_host, const float* evecs_x_host, int n1, const float* evecs_y_host, int n2,
                      int k, const float* cad_host, int ncad, const float* pc_host, int npc, const float thr[4],
                      unsigned flags, int64_t* out_host, int32_t* count_host, int32_t* status_host);
+
+/* A stream of single-pair conversions with host buffers — the per-sample loop of scripts/eval.py:83-91 with `depth`
+ * pairs in flight.  The object owns three CUDA streams and `depth` staging slots (device + pinned memory, grow-only: a
+ * steady stream of pairs allocates nothing per submission) on the device that is current at creation.  submit_* enqueues
+ * the upload of the pair, its kernels and the download of its result and returns at once; when all slots are in flight
+ * it first completes the OLDEST submission.  A submission is complete — its out_host (and count_host / status_host)
+ * written — once *completed_out, the number of completed submissions counted in submission order, has passed it;
+ * flush completes everything in flight.  Input pointers must stay valid and unchanged until the submission is complete
+ * (pinned inputs keep the uploads asynchronous; pageable ones work).  Results are bit-identical to f2p_naive_host /
+ * f2p_spatial_host.  One object per host thread; out_host sizes as for the *_host calls below. */
+typedef struct F2PPairStream F2PPairStream;
+int f2p_pair_stream_create(int depth, F2PPairStream** stream_out);             /* depth 1..16 */
+int f2p_pair_stream_destroy(F2PPairStream* s);                                 /* flushes, then frees everything */
+int f2p_pair_stream_submit_naive(F2PPairStream* s, const float* C_host, const float* evecs_x_host, int n1,
+                                 const float* evecs_y_host, int n2, int k, unsigned flags, int64_t* out_host,
+                                 long long* completed_out);
+int f2p_pair_stream_submit_spatial(F2PPairStream* s, const float* C_host, const float* evecs_x_host, int n1,
+                                   const float* evecs_y_host, int n2, int k, const float* cad_host, int ncad,
+                                   const float* pc_host, int npc, const float thr[4], unsigned flags, int64_t* out_host,
+                                   int32_t* count_host, int32_t* status_host, long long* completed_out);
+int f2p_pair_stream_flush(F2PPairStream* s, long long* completed_out);
 
 /* Measured FP32 FMA throughput of this device with the kernel-2 instruction mix (packed fma.rn.f32x2):
  * runs ~ms of pure FMA work and returns TFLOP/s (roofline denominator next to the nominal figure). */

@@ -1064,3 +1064,43 @@ def test_blocked_host_pipeline_matches_the_one_shot_call(solvers, oracle, path, 
         assert not got.is_cuda and torch.equal(got, want), (xb, yb)
     got16 = naive_host_blocked(P.C12.unsqueeze(0), ex, P.evecs_y, int16_compat=True)
     assert torch.equal(got16, solvers.naive_fmap2pointmap(P.C12.cuda(), ex.cuda(), P.evecs_y.cuda(), int16_compat=True).cpu())
+
+
+def test_pair_stream_matches_single_calls_on_ragged_pairs(solvers):
+    """The eval loop as a stream (3 pairs in flight, staging slots reused and regrown): every result equals the single
+    call's, in order — pairs of different sizes and K-compatible shapes, a 3-D C12, an empty scene, FP64 inputs."""
+    from fmap2pointmap_solvers.pipeline import naive_pair_stream
+    from fmap2pointmap_solvers.synth import make_pair
+    shapes = [(700, 300, 20), (2500, 1100, 20), (90, 40, 20), (1500, 0, 20), (3000, 2000, 20), (700, 300, 20), (64, 1, 20)]
+    ps = [make_pair(n1, max(n2, 1), k, seed=300 + i) for i, (n1, n2, k) in enumerate(shapes)]
+    feed = []
+    for i, (P, (n1, n2, k)) in enumerate(zip(ps, shapes)):
+        C = P.C12.unsqueeze(0) if i % 2 else P.C12
+        ex = P.evecs_x.double() if i == 2 else (P.evecs_x.pin_memory() if i % 3 == 0 else P.evecs_x)
+        feed.append((C, ex, P.evecs_y[:n2]))
+    for depth in (1, 3):
+        got = list(naive_pair_stream(iter(feed), depth=depth))
+        assert len(got) == len(feed)
+        for (C, ex, ey), g in zip(feed, got):
+            want = solvers.naive_fmap2pointmap(C.cuda(), ex.float().cuda(), ey.cuda()).cpu()
+            assert not g.is_cuda and g.dtype == torch.int64 and torch.equal(g, want)
+
+
+def test_spatial_pair_stream_matches_single_calls(solvers):
+    """Spatial solver over the native pair stream: ragged samples, more samples than slots, every map equal to the
+    single call's (same survivors in the same order), including a sample whose thresholds leave nothing."""
+    from fmap2pointmap_solvers.pipeline import spatial_pair_stream
+    from fmap2pointmap_solvers.synth import make_pair
+    shapes = [(900, 333, 30), (2000, 800, 30), (400, 150, 30), (1200, 500, 30), (900, 333, 30)]
+    ps = [make_pair(n1, n2, k, seed=400 + i) for i, (n1, n2, k) in enumerate(shapes)]
+    diams = [p.diam_cad for p in ps]
+    diams[2] = diams[2] * 1e-6           # nothing survives
+    feed = [(p.C12, p.evecs_x, p.evecs_y, p.CAD, p.PC, d) for p, d in zip(ps, diams)]
+    for depth in (1, 2, 4):
+        got = list(spatial_pair_stream(iter(feed), depth=depth))
+        assert len(got) == len(feed)
+        for (C, ex, ey, cad, pc, d), g in zip(feed, got):
+            want = solvers.spacial_filtering_fmap2pointmap(C.cuda(), ex.cuda(), ey.cuda(), CAD=cad.cuda(), PC=pc.cuda(),
+                                                           diam_cad=d).cpu()
+            assert g.dtype == torch.int64 and g.shape == want.shape and torch.equal(g, want)
+    assert got[2].shape == (2, 0)
