@@ -115,3 +115,90 @@ def allgather_packed_maps(flat: torch.Tensor, counts: torch.Tensor, group=None) 
     else:
         all_wire.copy_(wire)
     return all_wire.to(torch.int64).view(world, P, width), all_counts.view(world, P)
+
+
+# ---- one huge pair over several GPUs ("single huge pair": shard V1, lexicographic (d, idx) minimum) ----------
+_KEY_NONE = torch.iinfo(torch.int64).max
+
+
+def row_cuts(n1: int, world_size: int) -> List[Tuple[int, int]]:
+    """Contiguous CAD-row ranges [lo, hi) per rank, boundaries on multiples of 128 (the kernels' row tile); high ranks
+    of a small problem may get an empty range."""
+    step = ((n1 + world_size - 1) // world_size + 127) // 128 * 128 if world_size > 0 else n1
+    return [(min(r * step, n1), min((r + 1) * step, n1)) for r in range(world_size)]
+
+
+def reduce_keys(keys: torch.Tensor, group=None) -> torch.Tensor:
+    """In-place minimum over the ranks of per-scene-point keys `bits(distance) << 32 | global row` (int64; distances are
+    non-negative, so the signed order is the (distance, row) order; `_KEY_NONE` = no candidate).  One all-reduce: the
+    result on every rank is the key of the nearest row over ALL ranks' rows, ties to the lowest global row."""
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(keys, op=dist.ReduceOp.MIN, group=group)
+    return keys
+
+
+def _local_keys_cuda(C12, ex_rows, evecs_y, row0, device):
+    """Exact keys of this rank's CAD rows against every scene point (csrc: f2p_project + f2p_nn_argmin_keys)."""
+    from . import _lib
+    lib = _lib.load()
+    with torch.cuda.device(device):
+        C = _lib.dev_f32(C12, device).contiguous()
+        ex = _lib.rowmajor_2d(_lib.dev_f32(ex_rows, device)).contiguous()
+        ey = _lib.rowmajor_2d(_lib.dev_f32(evecs_y, device)).contiguous()
+        n1, k, n2 = int(ex.shape[0]), int(C.shape[0]), int(ey.shape[0])
+        ld1, ld2 = max((n1 + 127) // 128 * 128, 128), (n2 + 127) // 128 * 128
+        keys = torch.full((ld2,), -1, dtype=torch.int64, device=device)                 # every byte 0xFF: no candidate
+        if n1 > 0:
+            st = _lib.stream_ptr(device)
+            xT = torch.empty((k, ld1), dtype=torch.float32, device=device); nx = torch.empty((ld1,), dtype=torch.float32, device=device)
+            yT = torch.empty((k, ld2), dtype=torch.float32, device=device); ny = torch.empty((ld2,), dtype=torch.float32, device=device)
+            pb = (lib.f2p_project_workspace_bytes() + 255) // 256 * 256
+            ws = _lib.workspace(device, pb + lib.f2p_nn_workspace_bytes(n1, n2, k, 0) + 1024)
+            _lib.check(lib.f2p_project(ex.data_ptr(), n1, k, k, C.data_ptr(), xT.data_ptr(), nx.data_ptr(), ld1,
+                                       ws.data_ptr(), pb, st), "f2p_project")
+            _lib.check(lib.f2p_project(ey.data_ptr(), n2, k, k, None, yT.data_ptr(), ny.data_ptr(), ld2, ws.data_ptr(), pb, st),
+                       "f2p_project")
+            wn = ws[pb:]
+            _lib.check(lib.f2p_nn_argmin_keys(xT.data_ptr(), nx.data_ptr(), n1, ld1, int(row0), yT.data_ptr(), ny.data_ptr(), n2,
+                                              ld2, k, keys.data_ptr(), wn.data_ptr(), wn.numel(), st), "f2p_nn_argmin_keys")
+        return keys[:n2]
+
+
+def naive_row_sharded(C12, evecs_x, evecs_y, group=None, int16_compat: bool = False, local_keys: Optional[Callable] = None,
+                      device=None) -> torch.Tensor:
+    """`naive_fmap2pointmap` for ONE pair with the CAD rows split over the ranks of `group` (strong scaling of a single
+    huge pair).  Every rank passes the same C12 [K,K] and evecs_y [V2,K] and the full evecs_x [V1,K] (only its
+    own row range `row_cuts(V1, world)[rank]` is read); rank r evaluates its rows against all scene points and keeps, per
+    scene point, the exact key (distance bits, GLOBAL row); one all-reduce(MIN) of the V2 keys makes every rank hold the
+    pair's arg-min — per-element distances do not depend on the split, so the int64 [2,V2] result is
+    bit-identical to the single-GPU call, ties to the lowest row.  `local_keys(C, ex_rows, ey, row0) -> int64 [V2]` replaces
+    the CUDA kernels in the CPU tests of the exchange."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    C = C12.squeeze(0) if C12.dim() == 3 else C12
+    n1, n2 = int(evecs_x.shape[0]), int(evecs_y.shape[0])
+    if n1 < 1:
+        raise RuntimeError("evecs_x has no rows (argmin of an empty dimension)")
+    lo, hi = row_cuts(n1, world)[rank]
+    if local_keys is None:
+        from . import _lib
+        if device is None:
+            device = _lib.cuda_device_for(evecs_x, evecs_y, C)
+        keys = _local_keys_cuda(C, evecs_x[lo:hi], evecs_y, lo, device)
+    else:
+        keys = local_keys(C, evecs_x[lo:hi], evecs_y, lo)
+    keys = torch.where(keys < 0, torch.full_like(keys, _KEY_NONE), keys)         # "no candidate" must lose the signed minimum
+    reduce_keys(keys, group)
+    if local_keys is None:
+        from . import _lib
+        lib = _lib.load()
+        out = torch.empty((2, n2), dtype=torch.int64, device=keys.device)
+        if n2 > 0:
+            with torch.cuda.device(keys.device):
+                _lib.check(lib.f2p_keys_to_map(keys.data_ptr(), n2, _lib.F2P_INT16_COMPAT if int16_compat else 0, out.data_ptr(),
+                                               _lib.stream_ptr(keys.device)), "f2p_keys_to_map")
+        return out
+    idx = torch.arange(n2, dtype=torch.int64, device=keys.device)
+    if int16_compat:
+        idx = ((idx + 32768) % 65536) - 32768
+    return torch.stack([keys & 0xFFFFFFFF, idx], 0)

@@ -548,12 +548,49 @@ def run_b200_arm(args, wl):
             other[name] = entry
             del s2, d2
             torch.cuda.empty_cache()
+        if ctx.world > 1:
+            other["large_row_sharded"] = strong_scaled_pair(ctx, wl)
         line["other_workloads"] = other
     if ctx.rank == 0:
         print(json.dumps(line), flush=True)
     if ctx.dist is not None:
         ctx.dist.barrier()
         ctx.dist.destroy_process_group()
+
+
+def strong_scaled_pair(ctx, wl, steps=10, warmup=3):
+    """ONE pair of the headline workload with its CAD rows split over all ranks (distributed.naive_row_sharded): every
+    rank evaluates n1/N rows against all scene points, one NCCL all-reduce(MIN) of the (distance, global row) keys returns
+    the pair's arg-min to every rank.  Strong scaling of a single huge pair; the exchange is inside the
+    timed region; rank 0 also checks the map against its own unsplit call."""
+    from fmap2pointmap_solvers import naive_fmap2pointmap
+    from fmap2pointmap_solvers.distributed import naive_row_sharded
+    dev, dist = ctx.dev, ctx.dist
+    n1, n2, k = wl["n1"], wl["n2"], wl["k"]
+    P = make_pairs(n1, n2, k, 1234, 1)[0]                       # the SAME pair on every rank
+    C, ex, ey = P.C12.to(dev), P.evecs_x.to(dev), P.evecs_y.to(dev)
+    for _ in range(warmup):
+        out = naive_row_sharded(C, ex, ey)
+    same = bool(torch.equal(out, naive_fmap2pointmap(C, ex, ey)))
+    torch.cuda.synchronize(dev)
+    dist.barrier()
+    torch.cuda.synchronize(dev)
+    total = 0.0
+    for _ in range(steps):
+        ctx.flush.fill_(1)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = naive_row_sharded(C, ex, ey)
+        e1.record()
+        e1.synchronize()
+        total += e0.elapsed_time(e1)
+    t = torch.tensor([total, 0.0 if same else 1.0], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t[0].item()) / steps
+    return {"workload": f"one pair of n1={n1} x n2={n2}, k={k}, naive solver, CAD rows split over {ctx.world} GPUs",
+            "scaling": "strong", "ms_per_pair": ms, "value": float(n1) * n2 / (ms * 1e-3) / 1e9, "unit": UNIT,
+            "exchange": f"all-reduce(MIN) of {n2} int64 keys per pair (NCCL), inside the timed region",
+            "identical_to_unsplit_call_on_every_rank": float(t[1].item()) == 0.0, "steps": steps}
 
 
 def tc_stats(ctx):

@@ -137,6 +137,70 @@ def _worker_packed(rank, world, port, q):
     dist.destroy_process_group()
 
 
+def _worker_rows(rank, world, port, q):
+    import numpy as np
+    import torch.distributed as dist
+    from fmap2pointmap_solvers.distributed import naive_row_sharded, row_cuts
+    from fmap2pointmap_solvers.synth import make_pair
+    from oracle import f2p_oracle as O
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+
+    def local_keys(C, ex_rows, ey, row0):
+        # stand-in for the CUDA kernels (this test is about the exchange): the oracle's arg-min over this rank's rows and
+        # the distance it belongs to, as the library's key  bits(distance) << 32 | global row
+        n2 = ey.shape[0]
+        if ex_rows.shape[0] == 0:
+            return torch.full((n2,), -1, dtype=torch.int64)
+        idx = torch.from_numpy(O.naive(C, ex_rows, ey, int16_compat=False)[0])
+        d = torch.cdist(ex_rows @ C.t(), ey)[idx, torch.arange(n2)]
+        return (d.view(torch.int32).to(torch.int64) << 32) | (idx + row0)
+
+    ok = True
+    try:
+        for n1, n2, k, seed in ((300, 77, 16, 1), (1000, 40, 8, 2), (100, 9, 8, 3)):      # the last: rank 1 gets no rows
+            P = make_pair(n1, n2, k, seed=seed)
+            ex = P.evecs_x.clone()
+            if n1 >= 300:
+                ex[n1 - 5] = ex[3]          # an exact duplicate in the other rank's range: the lowest global row must win
+            got = naive_row_sharded(P.C12.unsqueeze(0), ex, P.evecs_y, local_keys=local_keys)
+            want = torch.from_numpy(O.naive(P.C12, ex, P.evecs_y, int16_compat=False))
+            ok = ok and got.dtype == torch.int64 and torch.equal(got, want)
+        cuts = row_cuts(100, world)
+        ok = ok and cuts[0] == (0, 100) and cuts[1] == (100, 100)
+    except Exception:
+        import traceback
+        traceback.print_exc()
+        ok = False
+    q.put((rank, ok))
+    dist.destroy_process_group()
+
+
+def test_row_sharded_single_pair_gloo_world2():
+    """One pair, CAD rows split over two ranks, one all-reduce(MIN) of (distance, global row) keys (the
+    single-huge-pair extension): same map as the unsplit solver, ties across the split to the lowest row."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 33500 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_worker_rows, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(results) == [(0, True), (1, True)]
+
+
+def test_row_cuts_cover_all_rows_on_tile_boundaries():
+    from fmap2pointmap_solvers.distributed import row_cuts
+    for n in (1, 127, 128, 129, 5000, 100000):
+        for w in (1, 2, 3, 8):
+            cuts = row_cuts(n, w)
+            assert len(cuts) == w and cuts[0][0] == 0 and cuts[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(cuts, cuts[1:])) and all(lo % 128 == 0 or lo == n for lo, _ in cuts)
+
+
 def test_packed_map_allgather_gloo_world2():
     """Counts first, then only the used prefix of every pair's result slots, int32 on the wire."""
     import torch.multiprocessing as mp
