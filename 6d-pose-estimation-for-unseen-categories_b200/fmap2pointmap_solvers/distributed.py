@@ -148,7 +148,7 @@ def _local_keys_cuda(C12, ex_rows, evecs_y, row0, device):
         n1, k, n2 = int(ex.shape[0]), int(C.shape[0]), int(ey.shape[0])
         ld1, ld2 = max((n1 + 127) // 128 * 128, 128), (n2 + 127) // 128 * 128
         keys = torch.full((ld2,), -1, dtype=torch.int64, device=device)                 # every byte 0xFF: no candidate
-        if n1 > 0:
+        if n1 > 0 and n2 > 0:                                                           # an empty block has nothing to add
             st = _lib.stream_ptr(device)
             xT = torch.empty((k, ld1), dtype=torch.float32, device=device); nx = torch.empty((ld1,), dtype=torch.float32, device=device)
             yT = torch.empty((k, ld2), dtype=torch.float32, device=device); ny = torch.empty((ld2,), dtype=torch.float32, device=device)
@@ -164,30 +164,51 @@ def _local_keys_cuda(C12, ex_rows, evecs_y, row0, device):
         return keys[:n2]
 
 
+def block_grid(n1: int, n2: int, world_size: int, col_weight: float = 2.0) -> Tuple[int, int]:
+    """(row shards R, column shards Cg), R * Cg = world: every rank gets the same n1*n2/world distance evaluations whatever
+    the grid, so the choice minimises what does NOT shrink with the other dimension — per-row work (projection, packing)
+    ~ n1/R plus per-scene-point work (transposition, packing, thresholds, exact verification) ~ col_weight * n2/Cg."""
+    best, best_cost = (world_size, 1), None
+    for r in range(1, world_size + 1):
+        if world_size % r:
+            continue
+        c = world_size // r
+        cost = n1 / r + col_weight * n2 / c
+        if best_cost is None or cost < best_cost:
+            best, best_cost = (r, c), cost
+    return best
+
+
 def naive_row_sharded(C12, evecs_x, evecs_y, group=None, int16_compat: bool = False, local_keys: Optional[Callable] = None,
-                      device=None) -> torch.Tensor:
-    """`naive_fmap2pointmap` for ONE pair with the CAD rows split over the ranks of `group` (strong scaling of a single
-    huge pair).  Every rank passes the same C12 [K,K] and evecs_y [V2,K] and the full evecs_x [V1,K] (only its
-    own row range `row_cuts(V1, world)[rank]` is read); rank r evaluates its rows against all scene points and keeps, per
-    scene point, the exact key (distance bits, GLOBAL row); one all-reduce(MIN) of the V2 keys makes every rank hold the
-    pair's arg-min — per-element distances do not depend on the split, so the int64 [2,V2] result is
-    bit-identical to the single-GPU call, ties to the lowest row.  `local_keys(C, ex_rows, ey, row0) -> int64 [V2]` replaces
-    the CUDA kernels in the CPU tests of the exchange."""
+                      device=None, grid: Optional[Tuple[int, int]] = None) -> torch.Tensor:
+    """`naive_fmap2pointmap` for ONE pair split over the ranks of `group` (strong scaling of a single huge pair, SURVEY
+    8(e)).  Every rank passes the same C12 [K,K], evecs_x [V1,K] and evecs_y [V2,K].  The ranks form an R x Cg grid
+    (`grid`, default `block_grid`): rank r = (r // Cg, r % Cg) evaluates the CAD rows `row_cuts(V1, R)[r // Cg]` against
+    the scene points `row_cuts(V2, Cg)[r % Cg]` and keeps, per scene point, the exact key (distance bits, GLOBAL row);
+    scene points outside its block stay "no candidate".  ONE all-reduce(MIN) of the V2 keys then both merges the row
+    shards and assembles the column shards: every rank holds the pair's arg-min.  Per-element distances do not depend on
+    the split, so the int64 [2,V2] result is bit-identical to the single-GPU call, ties to the lowest
+    row.  `local_keys(C, ex_rows, ey_cols, row0) -> int64 [cols]` replaces the CUDA kernels in the CPU tests."""
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     C = C12.squeeze(0) if C12.dim() == 3 else C12
     n1, n2 = int(evecs_x.shape[0]), int(evecs_y.shape[0])
     if n1 < 1:
         raise RuntimeError("evecs_x has no rows (argmin of an empty dimension)")
-    lo, hi = row_cuts(n1, world)[rank]
+    R, Cg = grid if grid is not None else block_grid(n1, n2, world)
+    if R * Cg != world:
+        raise ValueError(f"grid {R} x {Cg} does not match the {world} ranks of the group")
+    lo, hi = row_cuts(n1, R)[rank // Cg]
+    c0, c1 = row_cuts(n2, Cg)[rank % Cg]
     if local_keys is None:
         from . import _lib
         if device is None:
             device = _lib.cuda_device_for(evecs_x, evecs_y, C)
-        keys = _local_keys_cuda(C, evecs_x[lo:hi], evecs_y, lo, device)
+        part = _local_keys_cuda(C, evecs_x[lo:hi], evecs_y[c0:c1], lo, device)
     else:
-        keys = local_keys(C, evecs_x[lo:hi], evecs_y, lo)
-    keys = torch.where(keys < 0, torch.full_like(keys, _KEY_NONE), keys)         # "no candidate" must lose the signed minimum
+        part = local_keys(C, evecs_x[lo:hi], evecs_y[c0:c1], lo)
+    keys = torch.full((n2,), _KEY_NONE, dtype=torch.int64, device=part.device)
+    keys[c0:c1] = torch.where(part < 0, torch.full_like(part, _KEY_NONE), part)   # "no candidate" must lose the signed minimum
     reduce_keys(keys, group)
     if local_keys is None:
         from . import _lib

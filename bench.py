@@ -559,14 +559,15 @@ def run_b200_arm(args, wl):
 
 
 def strong_scaled_pair(ctx, wl, steps=10, warmup=3):
-    """ONE pair of the headline workload with its CAD rows split over all ranks (distributed.naive_row_sharded): every
-    rank evaluates n1/N rows against all scene points, one NCCL all-reduce(MIN) of the (distance, global row) keys returns
-    the pair's arg-min to every rank.  Strong scaling of a single huge pair; the exchange is inside the
+    """ONE pair of the headline workload split over all ranks as a grid of row x scene-point blocks
+    (distributed.naive_row_sharded): every rank evaluates its block, one NCCL all-reduce(MIN) of the (distance, global row)
+    keys merges the row shards, assembles the scene-point shards and returns the pair's arg-min to every rank.  Strong scaling of a single huge pair; the exchange is inside the
     timed region; rank 0 also checks the map against its own unsplit call."""
     from fmap2pointmap_solvers import naive_fmap2pointmap
-    from fmap2pointmap_solvers.distributed import naive_row_sharded
+    from fmap2pointmap_solvers.distributed import block_grid, naive_row_sharded
     dev, dist = ctx.dev, ctx.dist
     n1, n2, k = wl["n1"], wl["n2"], wl["k"]
+    grid = block_grid(n1, n2, ctx.world)
     P = make_pairs(n1, n2, k, 1234, 1)[0]                       # the SAME pair on every rank
     C, ex, ey = P.C12.to(dev), P.evecs_x.to(dev), P.evecs_y.to(dev)
     for _ in range(warmup):
@@ -587,7 +588,8 @@ def strong_scaled_pair(ctx, wl, steps=10, warmup=3):
     t = torch.tensor([total, 0.0 if same else 1.0], dtype=torch.float64, device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t[0].item()) / steps
-    return {"workload": f"one pair of n1={n1} x n2={n2}, k={k}, naive solver, CAD rows split over {ctx.world} GPUs",
+    return {"workload": f"one pair of n1={n1} x n2={n2}, k={k}, naive solver, split over {ctx.world} GPUs as "
+                        f"{grid[0]} CAD-row shards x {grid[1]} scene-point shards",
             "scaling": "strong", "ms_per_pair": ms, "value": float(n1) * n2 / (ms * 1e-3) / 1e9, "unit": UNIT,
             "exchange": f"all-reduce(MIN) of {n2} int64 keys per pair (NCCL), inside the timed region",
             "identical_to_unsplit_call_on_every_rank": float(t[1].item()) == 0.0, "steps": steps}

@@ -163,9 +163,10 @@ def _worker_rows(rank, world, port, q):
             ex = P.evecs_x.clone()
             if n1 >= 300:
                 ex[n1 - 5] = ex[3]          # an exact duplicate in the other rank's range: the lowest global row must win
-            got = naive_row_sharded(P.C12.unsqueeze(0), ex, P.evecs_y, local_keys=local_keys)
             want = torch.from_numpy(O.naive(P.C12, ex, P.evecs_y, int16_compat=False))
-            ok = ok and got.dtype == torch.int64 and torch.equal(got, want)
+            for grid in (None, (2, 1), (1, 2)):          # rows split, scene points split
+                got = naive_row_sharded(P.C12.unsqueeze(0), ex, P.evecs_y, local_keys=local_keys, grid=grid)
+                ok = ok and got.dtype == torch.int64 and torch.equal(got, want)
         cuts = row_cuts(100, world)
         ok = ok and cuts[0] == (0, 100) and cuts[1] == (100, 100)
     except Exception:
@@ -193,7 +194,11 @@ def test_row_sharded_single_pair_gloo_world2():
 
 
 def test_row_cuts_cover_all_rows_on_tile_boundaries():
-    from fmap2pointmap_solvers.distributed import row_cuts
+    from fmap2pointmap_solvers.distributed import block_grid, row_cuts
+    for w in (1, 2, 4, 8):
+        r, c = block_grid(100000, 100000, w)
+        assert r * c == w
+    assert block_grid(100000, 100, 8) == (8, 1) and block_grid(100, 100000, 8) == (1, 8)
     for n in (1, 127, 128, 129, 5000, 100000):
         for w in (1, 2, 3, 8):
             cuts = row_cuts(n, w)

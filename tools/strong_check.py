@@ -33,17 +33,31 @@ dist.all_reduce(flag, op=dist.ReduceOp.MAX)
 P = make_pair(100000, 100000, 128, seed=1234)
 C, ex, ey = P.C12.to(dev), P.evecs_x.to(dev), P.evecs_y.to(dev)
 for _ in range(3):
-    naive_row_sharded(C, ex, ey)
+    naive_row_sharded(C, ex, ey, grid=(world, 1))
 torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record()
 for _ in range(10):
-    out = naive_row_sharded(C, ex, ey)
+    out = naive_row_sharded(C, ex, ey, grid=(world, 1))
 e1.record(); e1.synchronize()
 t = torch.tensor([e0.elapsed_time(e1) / 10], device=dev)
 dist.all_reduce(t, op=dist.ReduceOp.MAX)
+for R in (1, 2, 4, 8):          # every grid of this world: which split of rows x scene points is fastest
+    if world % R:
+        continue
+    g = (R, world // R)
+    same = bool(torch.equal(naive_row_sharded(C, ex, ey, grid=g), out))
+    torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+    e0.record()
+    for _ in range(10):
+        naive_row_sharded(C, ex, ey, grid=g)
+    e1.record(); e1.synchronize()
+    tg = torch.tensor([e0.elapsed_time(e1) / 10, 0.0 if same else 1.0], device=dev)
+    dist.all_reduce(tg, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        print(f"world {world}: grid {g[0]} row shards x {g[1]} scene shards: {tg[0].item():.3f} ms, identical {tg[1].item() == 0}", flush=True)
 from fmap2pointmap_solvers.distributed import _local_keys_cuda, row_cuts  # noqa: E402
-lo, hi = row_cuts(100000, world)[rank]
+lo, hi = row_cuts(100000, world)[rank]          # the all-rows split, for the exchange share
 torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
 e0.record()
 for _ in range(10):
