@@ -364,9 +364,12 @@ nn_tc_screen_kernel(const __grid_constant__ CUtensorMap mapXA, const __grid_cons
             if (cnt < CAP) { my_list[cnt * TILE] = ((u64)enc_f(v) << 32) | row; ++cnt; ++nrec; }
             else ovf = true;
             float u = __fadd_ru(v, Wt);
+            // most records of a settled column are in band but above its K-th upper bound: they cannot move the threshold
+            if (u < ub[K - 1]) {
 #pragma unroll
-            for (int r = 0; r < K; ++r) { const float t2 = ub[r]; const bool p = u < t2; ub[r] = p ? u : t2; u = p ? t2 : u; }
-            T = fminf(ub[K - 1], Tg);
+                for (int r = 0; r < K; ++r) { const float t2 = ub[r]; const bool p = u < t2; ub[r] = p ? u : t2; u = p ? t2 : u; }
+                T = fminf(ub[K - 1], Tg);
+            }
         };
 
         const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * CHUNKS * 32);

@@ -469,7 +469,7 @@ def measure_workload(ctx, name, wl, ppg, steps, warmup, e2e_steps):
     tc = 2.0 * n1 * n2 * k * ppg >= 8.0e9 and k >= 19
     if spatial:
         k2 = (4 if tc else 0) + 3               # [pack x, pack y, screen, verify] + gated + exact fallback + merge
-        launches = prep + k2 + 1 + 3 * 4        # + filter init + 3 x (vote, classify, verify, combine)
+        launches = prep + k2 + 1 + 3 * 5        # + filter init + 3 x (vote, ordered vote, classify, verify, combine)
     elif tc:
         launches = prep + 4 + 2                 # pack x, pack y, screen, verify + gated (flagged tiles) + finalise
     else:
