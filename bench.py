@@ -804,9 +804,12 @@ def roofline_section(ctx, wl, ppg=1, stages=None):
             clk = 1.9e9
             roof["filter"]["executed"] = {
                 "evaluations_per_step": ex_ev, "votes_skipped_per_step": stages.get("filter_votes_skipped_per_step"),
-                "warp_instructions_per_64_evaluations": 25, "sqrt_per_evaluation": 2,
+                "warp_instructions_per_64_evaluations": 25,
+                # one MUFU.SQRT per evaluation for A, B's is reused while the scene point repeats (5 candidates per
+                # scene point in round 0): 2.3 warp-level MUFU per 64 evaluations on the ncu source page = 1.15 each
+                "sqrt_per_evaluation": 1.15,
                 "issue_slot_fraction": (ex_ev / 64.0 * 25.0) / (vote_ms * 1e-3 * 4 * 148 * clk) if vote_ms > 0 else None,
-                "mufu_fraction_at_16_per_clk_sm": (2.0 * ex_ev) / (vote_ms * 1e-3 * 16 * 148 * clk) if vote_ms > 0 else None,
+                "mufu_fraction_at_16_per_clk_sm": (1.15 * ex_ev) / (vote_ms * 1e-3 * 16 * 148 * clk) if vote_ms > 0 else None,
                 "g_evaluations_per_s": ex_ev / (vote_ms * 1e-3) / 1e9 if vote_ms > 0 else None,
                 "assumed_sm_clock_hz": clk}
     return roof
