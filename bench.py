@@ -778,12 +778,27 @@ def roofline_section(ctx, wl, ppg=1, stages=None):
         roof["stages"] = stages
         if ppg > 1 and sm["kernel2"] > 0:
             # the launch the step really makes: all pairs of the batch in one grid
-            peak = tf32.value if tensor else packed.value
-            roof["single_pair_launch"] = {"achieved": achieved, "ms_per_launch": nm}
+            # the library picks the path from the flops of the whole launch: a batch of small pairs takes the tensor pipe
+            # where one of its pairs alone would not
+            batch_tensor = flops * ppg >= 8.0e9 and k >= 19
+            peak = tf32.value if batch_tensor else packed.value
+            roof["single_pair_launch"] = {"achieved": achieved, "ms_per_launch": nm, "bound": roof["bound"],
+                                          "peak": roof["peak"], "frac": roof["frac"], "kernel": roof["kernel"]}
             bat = flops * ppg / (sm["kernel2"] * 1e-3) / 1e12
-            roof.update({"achieved": bat, "frac": bat / peak, "algorithmic_flops_per_launch": flops * ppg,
-                         "ms_per_launch": sm["kernel2"], "ms_best": None,
-                         "timed": stages["timed"] + ": %d pairs per launch" % ppg})
+            if batch_tensor and not tensor:
+                roof["kernel"] = ("nn_tc_screen_kernel<%d> + nn_tc_verify_kernel (tcgen05 TF32 screen with a proven error "
+                                  "band, exact FP32 re-evaluation of in-band candidates; %s), all pairs of the batch in one "
+                                  "grid" % (5 if top5 else 1, "top-5" if top5 else "arg-min"))
+                roof["peak_source"] = ("measured live: tcgen05.mma kind::tf32 M128 N256 K8 from shared memory, no loads / "
+                                       "epilogue (f2p_measure_tf32_peak)")
+                roof["candidates"] = tc_stats(ctx)
+            roof.update({"bound": "tensor" if batch_tensor else "fp32", "peak": peak, "achieved": bat, "frac": bat / peak,
+                         "algorithmic_flops_per_launch": flops * ppg, "ms_per_launch": sm["kernel2"], "ms_best": None,
+                         "timed": stages["timed"] + ": %d pairs per launch (operand packing + screen + verification + "
+                                  "FP32 pass over flagged tiles)" % ppg})
+            for stale in ("frac_nominal", "peak_nominal", "peak_scalar_ffma"):
+                if batch_tensor and not tensor:
+                    roof.pop(stale, None)
         if top5 and stages["filter_evals_per_step"] > 0:
             # kernel 3 = 21 flop per (a,b) evaluation of the reference x sum_r M_r^2, against the FP32 pipe;
             # `executed` = what the kernel really does: each unordered pair once (symmetry), nothing for a skipped round
