@@ -131,6 +131,10 @@ static int build_plan(const F2PPairDesc* d, int npairs, int k, int spatial, bool
         if (spatial && 5ll * d[i].n2 > 524288) { set_error("pair %d: 5*n2 > 524288 candidates unsupported", i); return F2P_ENOTSUP; }
         base_items += (d[i].n2 + TILE - 1) / TILE;
     }
+    // the tensor-pipe screen decides large calls; the FP32 kernels then only see the tiles it flags
+    double flops_all = 0.0;
+    for (int i = 0; i < npairs; ++i) flops_all += 2.0 * d[i].n1 * (double)d[i].n2 * k;
+    const bool tc_call = npairs > 0 && tc_enabled(flops_all, k, spatial);
     for (int i = 0; i < npairs; ++i) {
         PairDev& p = P.pairs[i];
         memset(&p, 0, sizeof(p));
@@ -139,7 +143,8 @@ static int build_plan(const F2PPairDesc* d, int npairs, int k, int spatial, bool
         p.n1 = d[i].n1; p.n2 = d[i].n2; p.ldx = d[i].ldx; p.ldy = d[i].ldy; p.ncad = d[i].ncad; p.npc = d[i].npc;
         memcpy(p.thr, d[i].thr, sizeof(p.thr));
         p.nrt = (p.n1 + TILE - 1) / TILE; p.nct = (p.n2 + TILE - 1) / TILE;
-        const int ns = choose_nsplit(base_items, p.nrt, sm_count(), spatial ? top5_min_tiles() : 16);
+        int ns = choose_nsplit(base_items, p.nrt, sm_count(), spatial ? top5_min_tiles() : 16);
+        if (tc_call) ns = fallback_nsplit(ns, base_items, sm_count());
         p.nsplit = ns;
         if (P.ld1_total + p.nrt * (int64_t)TILE > 0x7fffff00ll || P.ld2_total + p.nct * (int64_t)TILE > 0x7fffff00ll ||
             (int64_t)P.total_items + (int64_t)p.nct * ns > 0x7fffff00ll) {
@@ -158,7 +163,7 @@ static int build_plan(const F2PPairDesc* d, int npairs, int k, int spatial, bool
     }
     // tensor-pipe screen: its own row tiling (256-row tiles, one CTA per SM)
     P.spatial = spatial;
-    P.use_tc = npairs > 0 && tc_enabled(P.flops, k, spatial);
+    P.use_tc = tc_call;
     P.tc = TCPlan();
     if (P.use_tc) {
         int64_t rows = 0, items = 0, xt = 0;

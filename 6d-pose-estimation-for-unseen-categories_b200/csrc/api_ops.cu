@@ -89,7 +89,10 @@ static int nn_common(int mode, const float* xT, const float* nx, int n1, int ld1
     if (ws_bytes < f2p_nn_workspace_bytes(n1, n2, k, mode)) { set_error("workspace too small"); return F2P_ENOSPACE; }
     PairDev p;
     const int nrt = (n1 + TILE - 1) / TILE, nct = (n2 + TILE - 1) / TILE;
-    int rc = single_pair(p, n1, n2, ld1, ld2, pick_nsplit(nrt, nct));
+    int ns = pick_nsplit(nrt, nct);
+    // arg-min decided by the tensor-pipe screen: the FP32 launch only visits flagged tiles (its workspace does not depend on ns)
+    if (mode == 0 && ld2 == nct * TILE && tc_enabled(2.0 * n1 * (double)n2 * k, k, 0)) ns = fallback_nsplit(ns, nct, sm_count_now());
+    int rc = single_pair(p, n1, n2, ld1, ld2, ns);
     if (rc) return rc;
     if (mode == 0 && ld2 != nct * TILE) {
         set_error("f2p_nn_argmin needs ld2 == round_up(n2, %d) (the re-check operand shares the layout)", TILE);
@@ -198,7 +201,9 @@ int f2p_nn_argmin_keys(const float* xT, const float* nx, int n1, int ld1, int ro
     if (ws_bytes < f2p_nn_workspace_bytes(n1, n2, k, 0)) { set_error("workspace too small"); return F2P_ENOSPACE; }
     PairDev p;
     const int nrt = (n1 + TILE - 1) / TILE, nct = (n2 + TILE - 1) / TILE;
-    int rc = single_pair(p, n1, n2, ld1, ld2, pick_nsplit(nrt, nct));
+    int ns = pick_nsplit(nrt, nct);
+    if (tc_enabled(2.0 * n1 * (double)n2 * k, k, 0)) ns = fallback_nsplit(ns, nct, sm_count_now());
+    int rc = single_pair(p, n1, n2, ld1, ld2, ns);
     if (rc) return rc;
     if (ld2 != nct * TILE) { set_error("f2p_nn_argmin_keys needs ld2 == round_up(n2, %d)", TILE); return F2P_EINVAL; }
     unsigned char* ws = static_cast<unsigned char*>(ws_v);

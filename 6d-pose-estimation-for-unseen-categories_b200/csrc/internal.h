@@ -11,6 +11,16 @@ namespace f2p {
 // model — time ~ waves x (fixed per-CTA cost + row tiles per item), fixed ~ 1.5 tile times (descriptor fetch, barrier
 // init, column-operand load, first-tile bootstrap) — so that the grid fills whole waves: 18 splits = 288 CTAs = one
 // wave on 148 SMs instead of 20 splits = 320 CTAs = one wave plus a 24-CTA tail.
+// Row splits of the FP32 kernels when the tensor-pipe screen decides the call and they only run for the column tiles it
+// flags (usually none): every CTA of the launch still has to start and read its tile's flag, so the grid is kept at about
+// two waves instead of forty (cfg4: 782 instead of 11 730 CTAs, 47 -> 4 us per call); a flagged tile then streams more
+// row tiles per CTA.
+static inline int fallback_nsplit(int ns, long long base_items, int sm) {
+    if (base_items <= 0) return ns;
+    long long cap = (4ll * sm + base_items - 1) / base_items;
+    if (cap < 1) cap = 1;
+    return ns < cap ? ns : (int)cap;
+}
 static inline int choose_nsplit(long long base_items, int nrt, int sm, int min_tiles = 16) {
     if (base_items <= 0 || nrt <= 1) return 1;
     {   // F2P_NSPLIT: fixed split count for experiments (tools/)
