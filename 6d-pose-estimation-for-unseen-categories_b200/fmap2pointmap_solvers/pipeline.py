@@ -418,10 +418,11 @@ def naive_pair_stream(pairs, depth=3, int16_compat=False):
             ps.give_back(clean)
 
 
-def spatial_pair_stream(samples, depth=3, int16_compat=True):
+def spatial_pair_stream(samples, depth=3, int16_compat=True, verbose=True):
     """`spacial_filtering_fmap2pointmap` over a stream of host-resident samples (C12, evecs_x, evecs_y, CAD, PC,
-    diam_cad), `depth` in flight; yields, in order, the int64 [2,M'] host map of every sample ([2,0] when the filter
-    leaves nothing), bit-identical to the single call."""
+    diam_cad), `depth` in flight; yields, in order, the int64 [2,M'] host map of every sample, bit-identical to the single
+    call — including its side effects: "skipped" is printed and [2,0] returned when the filter leaves nothing
+    (spacial_filtering.py:70-71), and a candidate index outside CAD / PC raises IndexError."""
     import ctypes
     from .batched import _squeeze_c, thresholds
     device = _device()
@@ -429,7 +430,11 @@ def spatial_pair_stream(samples, depth=3, int16_compat=True):
 
     def result(item):
         out, meta = item[0], item[1]
-        m = int(meta[0])
+        m, status = int(meta[0]), int(meta[1])
+        if status & 2:
+            raise IndexError(f"candidate index out of range of CAD/PC (CAD rows {item[5].shape[0]}, PC rows {item[6].shape[0]})")
+        if status & 1 and verbose:
+            print("skipped")
         return out[:2 * m].view(2, m).clone() if m else torch.empty((2, 0), dtype=torch.int64)
 
     with torch.cuda.device(device):

@@ -1104,3 +1104,29 @@ def test_spatial_pair_stream_matches_single_calls(solvers):
                                                            diam_cad=d).cpu()
             assert g.dtype == torch.int64 and g.shape == want.shape and torch.equal(g, want)
     assert got[2].shape == (2, 0)
+
+
+def test_pair_streams_fail_cleanly_and_recover(solvers, capsys):
+    """A bad sample in the middle of a stream raises (after the earlier results were delivered), an abandoned generator
+    leaves nothing behind, and the next stream on the same thread works; the spatial stream prints "skipped" like the
+    single call and raises IndexError for a CAD that is shorter than the eigenbasis."""
+    from fmap2pointmap_solvers.pipeline import naive_pair_stream, spatial_pair_stream
+    from fmap2pointmap_solvers.synth import make_pair
+    P = make_pair(600, 200, 20, seed=77)
+    good = (P.C12, P.evecs_x, P.evecs_y)
+    bad = (P.C12, P.evecs_x[:, :19], P.evecs_y)
+    want = solvers.naive_fmap2pointmap(P.C12.cuda(), P.evecs_x.cuda(), P.evecs_y.cuda()).cpu()
+    got = []
+    with pytest.raises(RuntimeError):
+        for r in naive_pair_stream(iter([good, good, bad, good]), depth=2):
+            got.append(r)
+    assert all(torch.equal(r, want) for r in got)
+    it = naive_pair_stream(iter([good] * 5), depth=3)
+    assert torch.equal(next(it), want)
+    it.close()                                             # abandoned with pairs in flight
+    assert all(torch.equal(r, want) for r in naive_pair_stream(iter([good] * 4), depth=3))
+    capsys.readouterr()
+    res = list(spatial_pair_stream(iter([(P.C12, P.evecs_x, P.evecs_y, P.CAD, P.PC, P.diam_cad * 1e-6)])))
+    assert res[0].shape == (2, 0) and "skipped" in capsys.readouterr().out
+    with pytest.raises(IndexError):
+        list(spatial_pair_stream(iter([(P.C12, P.evecs_x, P.evecs_y, P.CAD[:300], P.PC, P.diam_cad)])))
