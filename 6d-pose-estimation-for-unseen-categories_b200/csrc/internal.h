@@ -106,7 +106,7 @@ int launch_tc(int top5, const float* xT, int64_t ld1_total, const float* nx, con
               const float* ny, int k, const PairDev* pairs_dev, int npairs, int uniform_tc_items, int total_tc_items,
               int uniform_tc_xtiles, int total_tc_xtiles, int uniform_ytiles, int total_ytiles, int64_t ld1_tc_total,
               unsigned flags, unsigned long long* best, int64_t* out5, int cand_is_out_layout, const TCWs& w,
-              cudaStream_t stream);
+              cudaStream_t stream, const unsigned long long* seed_keys = nullptr);
 // Row splits per column tile of the screen (one CTA per SM, each owning all of TMEM): whole waves on `sm` SMs, every
 // item streaming >= 8 tiles of 256 rows when the problem allows (per-CTA fixed cost ~ 2.5 tile times: TMEM allocation,
 // barrier init, the resident scene tile, pipeline fill and drain).

@@ -1101,7 +1101,8 @@ int launch_argmin_keys(const float* xT, int64_t ld1, const float* nx, const floa
     argmin_init_kernel<<<(unsigned)((ld2 + 255) / 256), 256, 0, stream>>>(w.best, nullptr, nullptr, (size_t)ld2, nullptr, 0, nullptr);
     if (tc) {
         if ((rc = launch_tc(0, xT, ld1, nx, yT, ld2, ny, k, pair_dev, 1, tc->uni_items, tc->total_items, tc->uni_xtiles,
-                            tc->total_xtiles, ytiles, ytiles, tc->ld1_tc_total, F2P_ROW0_ONLY, w.best, nullptr, 0, tc->ws, stream))) return rc;
+                            tc->total_xtiles, ytiles, ytiles, tc->ld1_tc_total, F2P_ROW0_ONLY, w.best, nullptr, 0, tc->ws, stream,
+                            keys))) return rc;          // the keys held so far seed the screen's thresholds
         prm.ncols = tc->ws.tcflag;
     }
     if ((rc = launch_gated<1>(xT, ld1, yT, ld2, k, prm, items, stream))) return rc;

@@ -711,7 +711,7 @@ __global__ void __launch_bounds__(256)
 tc_pack_kernel(const float* __restrict__ srcT, int64_t ld_total, const float* __restrict__ nrm,
                const PairDev* __restrict__ pairs, int npairs, int uniform_tiles, int k, int kp, float one_minus_eps,
                float* __restrict__ dst, float* __restrict__ dst_exact, uint32_t* __restrict__ nxmax, uint32_t* __restrict__ tau,
-               int* __restrict__ pair_bad) {
+               int* __restrict__ pair_bad, const u64* __restrict__ seed_keys) {
     __shared__ float s[TC_KB * PACK_LD];
     __shared__ float s_aug[3][TILE];
     __shared__ float s_live[TILE];
@@ -755,7 +755,20 @@ tc_pack_kernel(const float* __restrict__ srcT, int64_t ld_total, const float* __
             for (int o = 16; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
             if (lane == 0 && m > 0.f) atomicMax(nxmax + (dst_row0 / TC_N), __float_as_uint(m));
         } else {
-            tau[dst_row0 + tid] = ENC_INF;
+            // Threshold at the start of the scan.  A caller that already holds an exact (distance, row) key per scene point
+            // from other CAD rows of the same pair (blocked arg-min) passes it: a row of this call matters only if its
+            // rounded distance is <= the held one, i.e. c < (d + 1 ulp)^2 <= T0, and LB <= c, so the strict gate LB < T0
+            // keeps every such row (the same bound the FP32 kernel uses for its threshold).
+            uint32_t t0 = ENC_INF;
+            if (seed_keys && live) {                  // keys exist for the n2 scene points only, not for the padding
+                const u64 key = seed_keys[dst_row0 + tid];
+                const float d = __uint_as_float((uint32_t)(key >> 32));
+                if (key != ~0ull && d >= 0.f && d < 3.0e38f) {
+                    const float dn = __uint_as_float(__float_as_uint(d) + 1u);
+                    t0 = enc_f(__fmul_ru(dn, dn));
+                }
+            }
+            tau[dst_row0 + tid] = t0;
         }
     }
     const int nkb = (kp + TC_KB - 1) / TC_KB;
@@ -1009,7 +1022,8 @@ static int launch_screen(const TCWs& w, const CUtensorMap& mapXA, const CUtensor
 int launch_tc(int top5, const float* xT, int64_t ld1_total, const float* nx, const float* yT, int64_t ld2_total,
               const float* ny, int k, const PairDev* pairs_dev, int npairs, int uniform_tc_items, int total_tc_items,
               int uniform_tc_xtiles, int total_tc_xtiles, int uniform_ytiles, int total_ytiles, int64_t ld1_tc_total,
-              unsigned flags, u64* best, int64_t* out5, int cand_is_out_layout, const TCWs& w, cudaStream_t stream) {
+              unsigned flags, u64* best, int64_t* out5, int cand_is_out_layout, const TCWs& w, cudaStream_t stream,
+              const u64* seed_keys) {
     if (total_tc_items <= 0 || total_ytiles <= 0) return 0;
     const int kp = tc_kp(k);
     const double eps = tc_eps(k);
@@ -1021,9 +1035,9 @@ int launch_tc(int top5, const float* xT, int64_t ld1_total, const float* nx, con
     F2P_CUDA(cudaMemsetAsync(w.zero_base, 0, w.zero_bytes, stream));
     g_last_stats = w.stats;
     tc_pack_kernel<true><<<total_tc_xtiles, 256, 0, stream>>>(xT, ld1_total, nx, pairs_dev, npairs, uniform_tc_xtiles, k, kp,
-                                                             ome, w.XA, w.XR, w.nxmax, nullptr, w.pair_bad);
+                                                             ome, w.XA, w.XR, w.nxmax, nullptr, w.pair_bad, nullptr);
     tc_pack_kernel<false><<<total_ytiles, 256, 0, stream>>>(yT, ld2_total, ny, pairs_dev, npairs, uniform_ytiles, k, kp,
-                                                           ome, w.YA, nullptr, nullptr, w.tau, w.pair_bad);
+                                                           ome, w.YA, nullptr, nullptr, w.tau, w.pair_bad, seed_keys);
     F2P_CUDA(cudaGetLastError());
 
     CUtensorMap mapXA, mapYA;

@@ -107,7 +107,8 @@ int f2p_nn_top5(const float* xT_dev, const float* nx_dev, int n1, int ld1,
  * computation (naive.py:33-34 evaluated block by block; fmap2pointmap_solvers/pipeline.py: naive_host_blocked).
  * keys_dev[j] (u64, j < n2; set every byte to 0xFF before the first block) = min over the blocks processed so far of
  * (bits(d_ij) << 32 | row0 + i): merging by (distance, global row) keeps the reference's lowest-index rule for exact ties
- * across blocks, in whatever order they arrive.  xT / nx describe the block's n1 rows (global rows row0 .. row0 + n1 - 1),
+ * across blocks, in whatever order they arrive; the keys held on entry also seed the thresholds of the block's scan, so
+ * later row blocks of a scene block record only rows that can still win.  xT / nx describe the block's n1 rows (global rows row0 .. row0 + n1 - 1),
  * yT / ny its n2 scene points; workspace as for f2p_nn_argmin (f2p_nn_workspace_bytes(n1, n2, k, 0)). */
 int f2p_nn_argmin_keys(const float* xT_dev, const float* nx_dev, int n1, int ld1, int row0,
                        const float* yT_dev, const float* ny_dev, int n2, int ld2, int k,
