@@ -244,6 +244,12 @@ def _naive_single_host(lib, device, C12, evecs_x, evecs_y, int16_compat):
     n1, n2 = int(ex.shape[0]), int(ey.shape[0])
     if n1 < 1:
         raise RuntimeError("pair 0: evecs_x has no rows (argmin of an empty dimension)")
+    if float(n1) * n2 >= 2e9:
+        # one huge pair: its upload takes about as long as its kernels, so it goes through the blocked pipeline (row /
+        # column blocks, uploads behind the kernels); the result is the same map
+        from .pipeline import naive_host_blocked
+        with torch.cuda.device(device):
+            return naive_host_blocked(C, ex, ey, int16_compat=int16_compat).clone()
     out = torch.empty((2, n2), dtype=torch.int64)
     if n2 > 0:
         with torch.cuda.device(device):
