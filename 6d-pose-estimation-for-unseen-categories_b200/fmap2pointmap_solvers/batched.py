@@ -4,7 +4,7 @@
 """
 import ctypes
 import os
-from typing import List, Optional, Sequence
+from typing import List, Sequence
 
 import torch
 

@@ -8,7 +8,7 @@ These helpers write and read exactly that layout for a whole batch of solver out
 feeds the pose scripts unchanged.  Plain torch serialization; no arithmetic happens here.
 """
 import os
-from typing import Iterable, List, Sequence
+from typing import List, Sequence
 
 import torch
 

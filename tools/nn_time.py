@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Times kernel 2 alone (f2p_nn_argmin / f2p_nn_top5) under experiment switches: python tools/nn_time.py n1 n2 k top5 VAR..."""
-import ctypes, os, sys
+import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "6d-pose-estimation-for-unseen-categories_b200"))
 import torch
