@@ -1130,3 +1130,45 @@ def test_pair_streams_fail_cleanly_and_recover(solvers, capsys):
     assert res[0].shape == (2, 0) and "skipped" in capsys.readouterr().out
     with pytest.raises(IndexError):
         list(spatial_pair_stream(iter([(P.C12, P.evecs_x, P.evecs_y, P.CAD[:300], P.PC, P.diam_cad)])))
+
+
+@pytest.mark.parametrize("path", ["gated", "tc"])
+@pytest.mark.parametrize("gen,k", [("grid", 32), ("offset", 24), ("uniform", 20)])
+def test_blocked_and_sharded_argmin_on_tie_dense_inputs(solvers, oracle, path, gen, k, monkeypatch):
+    """Exact multi-way ties and cancellation-heavy inputs cut into row x column blocks: every later row block starts from
+    thresholds seeded by the keys its scene block already holds (T0 = up((d + 1 ulp)^2)), so a tie with a held best — in
+    the same sqrt_rn class, lower or higher row — must still be recorded and resolved by (distance, global row).  The same
+    keys path serves the multi-GPU row split (here on a world of one)."""
+    from fmap2pointmap_solvers.distributed import naive_row_sharded
+    from fmap2pointmap_solvers.pipeline import naive_host_blocked
+    from golden.cases import hard_inputs
+    monkeypatch.setenv("F2P_NN_PATH", path)
+    inp = hard_inputs(dict(n1=7000, n2=1500, k=k, seed=4242 + k, gen=gen))
+    C, ex, ey = inp["C12"], inp["evecs_x"], inp["evecs_y"]
+    want = oracle.naive(C, ex, ey, int16_compat=False)
+    one = solvers.naive_fmap2pointmap(C.cuda(), ex.cuda(), ey.cuda()).cpu().numpy()
+    np.testing.assert_array_equal(one, want)
+    for xb, yb in ((2, 2), (5, 1), (3, 2)):
+        np.testing.assert_array_equal(naive_host_blocked(C, ex, ey, xb=xb, yb=yb).numpy(), want, err_msg=f"{xb}x{yb}")
+    # row blocks arriving in DESCENDING order: the lower rows come last and must still win their ties
+    from fmap2pointmap_solvers import _lib
+    L = _lib.load(); dev = torch.device("cuda", torch.cuda.current_device()); st = _lib.stream_ptr(dev)
+    n1, n2 = ex.shape[0], ey.shape[0]
+    Cd, exd, eyd = C.cuda(), ex.cuda(), ey.cuda()
+    ld2 = (n2 + 127) // 128 * 128
+    yT = torch.empty(k, ld2, device=dev); ny = torch.empty(ld2, device=dev)
+    pb = (L.f2p_project_workspace_bytes() + 255) // 256 * 256
+    cuts = [(0, 2304), (2304, 4608), (4608, n1)]
+    ws = torch.empty(pb + max(L.f2p_nn_workspace_bytes(b - a, n2, k, 0) for a, b in cuts) + 1024, dtype=torch.uint8, device=dev)
+    _lib.check(L.f2p_project(eyd.data_ptr(), n2, k, k, None, yT.data_ptr(), ny.data_ptr(), ld2, ws.data_ptr(), pb, st), "f2p_project")
+    keys = torch.full((ld2,), -1, dtype=torch.int64, device=dev)
+    for a, b in reversed(cuts):
+        ld1 = (b - a + 127) // 128 * 128
+        xT = torch.empty(k, ld1, device=dev); nx = torch.empty(ld1, device=dev)
+        _lib.check(L.f2p_project(exd[a:b].data_ptr(), b - a, k, k, Cd.data_ptr(), xT.data_ptr(), nx.data_ptr(), ld1, ws.data_ptr(), pb, st), "f2p_project")
+        wn = ws[pb:]
+        _lib.check(L.f2p_nn_argmin_keys(xT.data_ptr(), nx.data_ptr(), b - a, ld1, a, yT.data_ptr(), ny.data_ptr(), n2, ld2, k,
+                                        keys.data_ptr(), wn.data_ptr(), wn.numel(), st), "f2p_nn_argmin_keys")
+    np.testing.assert_array_equal((keys[:n2] & 0xFFFFFFFF).cpu().numpy(), want[0])
+    got = naive_row_sharded(Cd, exd, eyd)                                 # not under torch.distributed: a world of one
+    np.testing.assert_array_equal(got.cpu().numpy(), want)
