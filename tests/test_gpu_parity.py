@@ -1172,3 +1172,23 @@ def test_blocked_and_sharded_argmin_on_tie_dense_inputs(solvers, oracle, path, g
     np.testing.assert_array_equal((keys[:n2] & 0xFFFFFFFF).cpu().numpy(), want[0])
     got = naive_row_sharded(Cd, exd, eyd)                                 # not under torch.distributed: a world of one
     np.testing.assert_array_equal(got.cpu().numpy(), want)
+
+
+def test_batch_mixing_screened_and_ordered_pairs(solvers, oracle):
+    """One batch, one launch sequence: pairs 0, 2, 3 vote through the screened kernel, pair 1 (every CAD vertex carries a
+    tiny nonzero coordinate, outside the packed square root's proven range) is left to the ordered kernel through its tile
+    list.  Every pair's survivors equal the oracle's; the ragged shapes make the pairs' tile counts differ."""
+    from fmap2pointmap_solvers.batched import spatial_batched
+    from fmap2pointmap_solvers.synth import make_pair
+    shapes = [(900, 333), (1200, 410), (700, 150), (1500, 600)]
+    ps = [make_pair(n1, n2, 30, seed=610 + i) for i, (n1, n2) in enumerate(shapes)]
+    cads = [p.CAD.clone() for p in ps]
+    cads[1][:, 1] = 1e-30 * (1.0 + torch.arange(cads[1].shape[0], dtype=torch.float32))
+    diams = [p.diam_cad * 2.5 for p in ps]                 # loose thresholds: all three rounds keep candidates
+    got = spatial_batched([p.C12.cuda() for p in ps], [p.evecs_x.cuda() for p in ps], [p.evecs_y.cuda() for p in ps],
+                          [c.cuda() for c in cads], [p.PC.cuda() for p in ps], diams, verbose=False)
+    for p, c, d, g in zip(ps, cads, diams, got):
+        want = oracle.spatial(p.C12, p.evecs_x, p.evecs_y, c, p.PC, d)
+        assert g.shape[1] == want.shape[1]
+        np.testing.assert_array_equal(g.cpu().numpy(), want)
+    assert sum(g.shape[1] for g in got) > 0
