@@ -547,10 +547,13 @@ nn_tc_verify_kernel(const TCVerifyParams prm) {
     const uint32_t tau = prm.tau[yc];
     s_ny[tid] = prm.ny[yc];
     s_best[tid] = ~0ull;
-    {   // stage the tile's scene columns: k independent coalesced loads per thread
+    {   // stage the tile's scene columns: k coalesced asynchronous copies per thread, all in flight at once (a register-
+        // staged loop kept eight in flight and paid k/8 memory round trips per CTA)
         const float* yp = prm.yT + yc;
-#pragma unroll 8
-        for (int c = 0; c < k; ++c) s_y[c * TILE + tid] = __ldg(yp + (int64_t)c * prm.ld2_total);
+        for (int c = 0; c < k; ++c)
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(s_y + c * TILE + tid)),
+                         "l"(yp + (int64_t)c * prm.ld2_total) : "memory");
+        asm volatile("cp.async.commit_group;" ::: "memory");
     }
     const int nsplit = pd->tc_nsplit;
     const int nlists = nsplit * prm.eh;
@@ -577,6 +580,95 @@ nn_tc_verify_kernel(const TCVerifyParams prm) {
             }
         }
     };
+    if constexpr (K == 1) {
+        // Arg-min: ONE pass.  A passing entry takes the next slot of the CTA's item arrays through a shared counter (the
+        // order of the items does not matter: keys merge with atomicMin); lists are read two at a time, both counts and
+        // then both lists' first eight entries in flight together, so a column's walk is a handful of L2 round trips
+        // instead of three per list and pass.  Entries beyond the item arrays' capacity are evaluated by their own thread.
+        __shared__ int s_n;
+        if (tid == 0) s_n = 0;
+        __syncthreads();
+        const int kr = (k + 3) & ~3, k4 = k & ~3;
+        int mine = 0, nviol = 0;
+        // one candidate in the reference's arithmetic (sequential-k fmaf, + nx, + ny, clamp, sqrt_rn)
+        auto eval_one = [&](uint32_t i0, int col, float lb) -> u64 {
+            const float* xp = prm.XR + ((int64_t)pd->xa_row0 + i0) * kr;
+            const float* yq = s_y + col;
+            float acc = 0.f;
+#pragma unroll 4
+            for (int c = 0; c < k4; c += 4) {
+                const float4 xv = __ldg(reinterpret_cast<const float4*>(xp + c));
+                acc = fmaf(xv.x, yq[c * TILE], acc);
+                acc = fmaf(xv.y, yq[(c + 1) * TILE], acc);
+                acc = fmaf(xv.z, yq[(c + 2) * TILE], acc);
+                acc = fmaf(xv.w, yq[(c + 3) * TILE], acc);
+            }
+            if (k4 < k) {
+                const float4 xv = __ldg(reinterpret_cast<const float4*>(xp + k4));
+                const float xa[3] = {xv.x, xv.y, xv.z};
+#pragma unroll
+                for (int t = 0; t < 3; ++t)
+                    if (k4 + t < k) acc = fmaf(xa[t], yq[(k4 + t) * TILE], acc);
+            }
+            const float v = __fadd_rn(__fadd_rn(acc, __ldg(prm.nx + pd->x_col0 + i0)), s_ny[col]);
+            if (lb > v) ++nviol;                           // the lower bound must hold: assumption A's run-time check
+            return tc_make_key(__fsqrt_rn(fmaxf(v, 0.f)), i0);
+        };
+        auto take = [&](u64 ce) {
+            ++mine;
+            const int slot = atomicAdd(&s_n, 1);
+            if (slot < VCAP) {
+                s_row[slot] = (uint32_t)(ce & 0xffffffffull);
+                s_lb[slot] = dec_f((uint32_t)(ce >> 32));
+                s_col[slot] = (uint16_t)tid;
+            } else {
+                asm volatile("cp.async.wait_all;" ::: "memory");    // this column of the scene tile was copied by this thread
+                atomicMin(&s_best[tid], eval_one((uint32_t)(ce & 0xffffffffull), tid, dec_f((uint32_t)(ce >> 32))));
+            }
+        };
+        for (int sh = 0; sh < nlists; sh += 2) {
+            const u64 *c0, *c1 = nullptr;
+            const int n0 = list_of(sh, c0);
+            const int n1 = (sh + 1 < nlists) ? list_of(sh + 1, c1) : 0;
+            for (int e0 = 0; e0 < n0 || e0 < n1; e0 += 8) {
+                u64 v0[8], v1[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    v0[u] = (e0 + u < n0) ? __ldg(c0 + (size_t)(e0 + u) * TILE) : ~0ull;
+                    v1[u] = (e0 + u < n1) ? __ldg(c1 + (size_t)(e0 + u) * TILE) : ~0ull;
+                }
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    if ((uint32_t)(v0[u] >> 32) < tau) take(v0[u]);
+                    if ((uint32_t)(v1[u] >> 32) < tau) take(v1[u]);
+                }
+            }
+        }
+        asm volatile("cp.async.wait_all;" ::: "memory");     // the scene tile (its copies ran behind the walk)
+        __syncthreads();
+        const int cnt = min(VCAP, s_n);
+        for (int w = tid; w < cnt; w += TILE) {
+            const int wn = w + TILE;
+            if (wn < cnt) {                                  // the next item's row towards L1 while this one computes
+                const float* q0 = prm.XR + ((int64_t)pd->xa_row0 + s_row[wn]) * kr;
+                for (int c = 0; c < kr; c += 32) prefetch_l1(q0 + c);
+            }
+            const int col = s_col[w];
+            atomicMin(&s_best[col], eval_one(s_row[w], col, s_lb[w]));
+        }
+        __syncthreads();
+        if (j < n2 && s_best[tid] != ~0ull) atomicMin(prm.best + yc, s_best[tid]);
+        if (prm.stats) {
+            int nv = mine, vi = nviol;
+#pragma unroll
+            for (int m = 16; m >= 1; m >>= 1) { nv += __shfl_xor_sync(0xffffffffu, nv, m); vi += __shfl_xor_sync(0xffffffffu, vi, m); }
+            if (lane == 0) {
+                if (nv) atomicAdd(prm.stats + 2, (unsigned long long)nv);
+                if (vi) atomicAdd(prm.stats + 3, (unsigned long long)vi);
+            }
+        }
+        return;
+    }
     // pass 0: how many entries of this column are below its final threshold
     int mine = 0;
     walk([&](u64) { ++mine; });
@@ -585,6 +677,7 @@ nn_tc_verify_kernel(const TCVerifyParams prm) {
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
     if (lane == 31) s_wsum[warp] = incl;
+    asm volatile("cp.async.wait_all;" ::: "memory");         // the scene tile (its copies ran behind the counting pass)
     __syncthreads();
     int offset = incl - mine, total = 0;
 #pragma unroll
