@@ -568,15 +568,25 @@ nn_tc_verify_kernel(const TCVerifyParams prm) {
     // dependent L2 round trip per entry was most of this kernel's time on short scans: ncu, 8 % issue utilisation).
     // Slots past the end read as ~0, whose encoded bound is above every threshold.
     auto walk = [&](auto&& visit) {
-        for (int sh = 0; sh < nlists; ++sh) {
-            const u64* cl; const int n = list_of(sh, cl);
-            for (int e0 = 0; e0 < n; e0 += 8) {
-                u64 v[8];
+        // two lists at a time: both counts, then eight entries of each in flight together; every walk visits the entries
+        // in the same order (the second walk relies on it)
+        for (int sh = 0; sh < nlists; sh += 2) {
+            const u64 *c0, *c1 = nullptr;
+            const int n0 = list_of(sh, c0);
+            const int n1 = (sh + 1 < nlists) ? list_of(sh + 1, c1) : 0;
+            for (int e0 = 0; e0 < n0 || e0 < n1; e0 += 8) {
+                u64 v0[8], v1[8];
 #pragma unroll
-                for (int u = 0; u < 8; ++u) v[u] = (e0 + u < n) ? __ldg(cl + (size_t)(e0 + u) * TILE) : ~0ull;
+                for (int u = 0; u < 8; ++u) {
+                    v0[u] = (e0 + u < n0) ? __ldg(c0 + (size_t)(e0 + u) * TILE) : ~0ull;
+                    v1[u] = (e0 + u < n1) ? __ldg(c1 + (size_t)(e0 + u) * TILE) : ~0ull;
+                }
 #pragma unroll
                 for (int u = 0; u < 8; ++u)
-                    if ((uint32_t)(v[u] >> 32) < tau) visit(v[u]);
+                    if ((uint32_t)(v0[u] >> 32) < tau) visit(v0[u]);
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    if ((uint32_t)(v1[u] >> 32) < tau) visit(v1[u]);
             }
         }
     };
