@@ -1,8 +1,9 @@
 // api_host.cu — host-buffer entry points: what a non-torch caller (C, C++, ctypes with numpy) binds.
 //
 // F2PPairStream is the per-sample loop of scripts/eval.py:83-91 as a small native executor: `depth` staging slots on the
-// device, three CUDA streams (uploads / kernels / downloads) and in-order completion into the caller's own buffers, so
-// pair i+1 is uploaded and pair i-1 downloaded while pair i computes.  Device and pinned memory is grow-only and owned by
+// device, an upload stream, a download stream and one kernel stream per slot, and in-order completion into the caller's
+// own buffers, so pair i+1 is uploaded and pair i-1 downloaded while pair i computes — and the kernels of small pairs in
+// flight overlap on the GPU (one 5k x 2k pair keeps the SMs busy 70 % of its 50 us).  Device and pinned memory is grow-only and owned by
 // the stream object: a steady stream of pairs allocates nothing per submission.  f2p_naive_host / f2p_spatial_host are
 // one submission + flush on a per-thread stream object of depth 1.
 #include <string.h>
@@ -19,6 +20,8 @@ struct F2PPairStream {
         float* in = nullptr;        size_t in_cap = 0;       // device staging: C | evecs_x | evecs_y | cad | pc (floats)
         int64_t* out_d = nullptr;   size_t out_cap = 0;      // device result slots (+ 2 int32 words: count, status)
         int64_t* out_h = nullptr;   size_t outh_cap = 0;     // pinned mirror of out_d
+        cudaStream_t comp = nullptr;                         // this slot's kernels: pairs in flight may overlap on the GPU
+        void* ws = nullptr;         size_t ws_cap = 0;       // (a small pair leaves most SMs idle), so each has its own workspace
         cudaEvent_t up = nullptr, kdone = nullptr, done = nullptr;
         bool busy = false;
         int64_t* user_out = nullptr; int32_t* user_count = nullptr; int32_t* user_status = nullptr;
@@ -26,9 +29,8 @@ struct F2PPairStream {
         bool spatial = false;
     };
     int device = 0, depth = 1;
-    cudaStream_t h2d = nullptr, comp = nullptr, d2h = nullptr;
+    cudaStream_t h2d = nullptr, d2h = nullptr;
     std::vector<Slot> slots;
-    void* ws = nullptr; size_t ws_cap = 0;
     long long submitted = 0, completed = 0;
 };
 
@@ -78,13 +80,13 @@ int grow(F2PPairStream* s, F2PPairStream::Slot& sl, size_t in_floats, size_t out
         F2P_CUDA(cudaMallocHost(&sl.out_h, sizeof(int64_t) * (need + need / 4)));
         sl.out_cap = need + need / 4;
     }
-    if (ws_bytes > s->ws_cap) {
-        F2P_CUDA(cudaStreamSynchronize(s->comp));            // earlier pairs still use the old workspace
-        if (s->ws) F2P_CUDA(cudaFree(s->ws));
-        s->ws = nullptr; s->ws_cap = 0;
-        F2P_CUDA(cudaMalloc(&s->ws, ws_bytes + ws_bytes / 4));
-        s->ws_cap = ws_bytes + ws_bytes / 4;
+    if (ws_bytes > sl.ws_cap) {                              // the slot's previous submission is complete: nothing uses it
+        if (sl.ws) F2P_CUDA(cudaFree(sl.ws));
+        sl.ws = nullptr; sl.ws_cap = 0;
+        F2P_CUDA(cudaMalloc(&sl.ws, ws_bytes + ws_bytes / 4));
+        sl.ws_cap = ws_bytes + ws_bytes / 4;
     }
+    (void)s;
     return 0;
 }
 
@@ -124,15 +126,15 @@ int submit(F2PPairStream* s, bool spatial, const float* C, const float* ex, int 
         F2P_TRY(up(oC, C, (size_t)k * k)); F2P_TRY(up(ox, ex, (size_t)n1 * k)); F2P_TRY(up(oy, ey, (size_t)n2 * k));
         if (spatial) { F2P_TRY(up(ocad, cad, 3 * (size_t)ncad)); F2P_TRY(up(opc, pc, 3 * (size_t)npc)); }
         F2P_CUDA(cudaEventRecord(sl.up, s->h2d));
-        F2P_CUDA(cudaStreamWaitEvent(s->comp, sl.up, 0));
+        F2P_CUDA(cudaStreamWaitEvent(sl.comp, sl.up, 0));
         int32_t* meta_d = reinterpret_cast<int32_t*>(sl.out_d + out_elems);
         if (spatial) {
             F2P_TRY(f2p_spatial_batched(sl.in + ox, sl.in + oy, sl.in + oC, sl.in + ocad, sl.in + opc, &d, 1, k, flags,
-                                        sl.out_d, meta_d, meta_d + 1, nullptr, s->ws, s->ws_cap, s->comp));
+                                        sl.out_d, meta_d, meta_d + 1, nullptr, sl.ws, sl.ws_cap, sl.comp));
         } else {
-            F2P_TRY(f2p_naive_batched(sl.in + ox, sl.in + oy, sl.in + oC, &d, 1, k, flags, sl.out_d, s->ws, s->ws_cap, s->comp));
+            F2P_TRY(f2p_naive_batched(sl.in + ox, sl.in + oy, sl.in + oC, &d, 1, k, flags, sl.out_d, sl.ws, sl.ws_cap, sl.comp));
         }
-        F2P_CUDA(cudaEventRecord(sl.kdone, s->comp));
+        F2P_CUDA(cudaEventRecord(sl.kdone, sl.comp));
         F2P_CUDA(cudaStreamWaitEvent(s->d2h, sl.kdone, 0));
         F2P_CUDA(cudaMemcpyAsync(sl.out_h, sl.out_d, sizeof(int64_t) * (out_elems + (spatial ? 1 : 0)), cudaMemcpyDeviceToHost, s->d2h));
     }
@@ -157,10 +159,10 @@ void release(F2PPairStream* s) {
         if (sl.up) cudaEventDestroy(sl.up);
         if (sl.kdone) cudaEventDestroy(sl.kdone);
         if (sl.done) cudaEventDestroy(sl.done);
+        if (sl.ws) cudaFree(sl.ws);
+        if (sl.comp) cudaStreamDestroy(sl.comp);
     }
-    if (s->ws) cudaFree(s->ws);
     if (s->h2d) cudaStreamDestroy(s->h2d);
-    if (s->comp) cudaStreamDestroy(s->comp);
     if (s->d2h) cudaStreamDestroy(s->d2h);
     delete s;
 }
@@ -173,11 +175,13 @@ int create(int depth, F2PPairStream** out) {
     auto fail = [&](cudaError_t e, const char* what) { set_error("%s failed: %s", what, cudaGetErrorString(e)); release(s); return (int)e; };
     cudaError_t e;
     if ((e = cudaGetDevice(&s->device)) != cudaSuccess) return fail(e, "cudaGetDevice");
-    for (cudaStream_t* st : {&s->h2d, &s->comp, &s->d2h})
+    for (cudaStream_t* st : {&s->h2d, &s->d2h})
         if ((e = cudaStreamCreateWithFlags(st, cudaStreamNonBlocking)) != cudaSuccess) return fail(e, "cudaStreamCreateWithFlags");
-    for (auto& sl : s->slots)
+    for (auto& sl : s->slots) {
+        if ((e = cudaStreamCreateWithFlags(&sl.comp, cudaStreamNonBlocking)) != cudaSuccess) return fail(e, "cudaStreamCreateWithFlags");
         for (cudaEvent_t* ev : {&sl.up, &sl.kdone, &sl.done})
             if ((e = cudaEventCreateWithFlags(ev, cudaEventDisableTiming)) != cudaSuccess) return fail(e, "cudaEventCreateWithFlags");
+    }
     *out = s;
     return 0;
 }

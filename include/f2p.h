@@ -231,8 +231,9 @@ int f2p_spatial_host(const float* C_host, const float* evecs_x_host, int n1, con
                      unsigned flags, int64_t* out_host, int32_t* count_host, int32_t* status_host);
 
 /* A stream of single-pair conversions with host buffers — the per-sample loop of scripts/eval.py:83-91 with `depth`
- * pairs in flight.  The object owns three CUDA streams and `depth` staging slots (device + pinned memory, grow-only: a
- * steady stream of pairs allocates nothing per submission) on the device that is current at creation.  submit_* enqueues
+ * pairs in flight.  The object owns an upload stream, a download stream and `depth` staging slots, each with its own
+ * kernel stream and workspace (device + pinned memory, grow-only: a steady stream of pairs allocates nothing per
+ * submission; the kernels of small pairs in flight overlap on the GPU) on the device that is current at creation.  submit_* enqueues
  * the upload of the pair, its kernels and the download of its result and returns at once; when all slots are in flight
  * it first completes the OLDEST submission.  A submission is complete — its out_host (and count_host / status_host)
  * written — once *completed_out, the number of completed submissions counted in submission order, has passed it;
